@@ -1,0 +1,260 @@
+// Shared device helpers for libb200ep (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp8.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/b200ep.h"
+
+#ifndef __CUDA_ARCH__
+#define B200EP_HOST 1
+#endif
+
+namespace b200ep {
+
+constexpr int kMaxRanks = B200EP_MAX_RANKS;
+constexpr int kMaxLocalExperts = B200EP_MAX_LOCAL_EXPERTS;
+constexpr int kMaxTopk = B200EP_MAX_TOPK;
+constexpr int kNumSlots = B200EP_NUM_SLOTS;
+constexpr int kGroup = 128;  // FP8 quantisation group (DEEPEP_QUANT_BLOCK_SIZE, deepep_ll.py:28)
+
+// ---- symmetric control block (first kCtrlBytes of every rank's region; peers write it)
+enum FlagCat { kFlagHtNotify = 0, kFlagHtData, kFlagHtComb, kFlagLlCount, kFlagLlData, kFlagLlComb, kNumFlagCat };
+constexpr size_t kFlagStride = 128;  // one flag per 128-byte line
+constexpr size_t kCtrlFlagsOff = 0;
+constexpr size_t kCtrlFlagsBytes = (size_t)kNumFlagCat * kNumSlots * kMaxRanks * kFlagStride;
+constexpr size_t kCtrlHtCntRankOff = 16384;  // int32 [slot][src][kMaxRanks]
+constexpr size_t kCtrlHtCntExpOff = 32768;   // int32 [slot][src][kMaxLocalExperts]
+constexpr size_t kCtrlLlCntOff = kCtrlHtCntExpOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 4;
+constexpr size_t kCtrlBytes = 1 << 20;
+static_assert(kCtrlFlagsBytes <= kCtrlHtCntRankOff, "flags overflow");
+static_assert(kCtrlLlCntOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 4 <= kCtrlBytes, "ctrl overflow");
+
+__host__ __device__ inline size_t flag_off(int cat, int slot, int src) {
+  return kCtrlFlagsOff + (((size_t)cat * kNumSlots + slot) * kMaxRanks + src) * kFlagStride;
+}
+
+// ---- per-slot metadata in PRIVATE device memory (never written by peers)
+struct HtMeta {
+  int32_t rank_prefix[kMaxRanks + 1];  // rows [p[s], p[s+1]) of my receive region came from rank s
+  int32_t send_base[kMaxRanks];        // first row I own in rank d's receive region
+  int32_t num_recv;
+  int32_t pad[5];
+  int32_t recv_per_expert[kMaxLocalExperts];
+};
+
+struct Peers {
+  char* base[kMaxRanks];
+};
+
+// Region layout of one high-throughput slot (identical on every rank).
+struct HtPlan {
+  size_t off_x, off_scales, off_idx, off_w, off_src, off_stage;
+  int t_cap;       // tokens per rank the slot can take
+  int cap_rows;    // world * t_cap receive rows
+  int row_bytes;   // payload bytes per token (H for fp8, 2H for bf16)
+  int scale_bytes; // H/128*4 or 0
+  int H, K, x_kind;
+};
+
+// Region layout of one low-latency slot.
+struct LlPlan {
+  size_t off_x, off_scales, off_src, off_stage;
+  int cap;  // world * max_tok slots per local expert
+  int e_local;
+  int row_bytes, scale_bytes;
+  int H, K, max_tok, use_fp8;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint64_t ld_acquire_sys_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u64(uint64_t* p, uint64_t v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t ld_acquire_gpu_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u64(uint64_t* p, uint64_t v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ int4 ld_nc_v4(const void* p) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ int4 ld_cg_v4(const void* p) {  // L2 only: data written by peers / other kernels
+  int4 r;
+  asm volatile("ld.global.cg.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_na_v4(void* p, const int4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// TMA bulk copy shared -> global (local or peer), tracked by the thread's bulk async-group.
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all of this thread's groups have finished READING shared memory (buffer reusable)
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all of this thread's groups are complete (writes performed)
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// order this thread's generic-proxy shared-memory writes before later async-proxy (TMA) reads
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// Spin until *flag >= want (flag written by another GPU).  Traps instead of hanging forever.
+__device__ __forceinline__ void wait_flag_sys(const uint64_t* flag, uint64_t want, int what, int me, int peer) {
+  long long t0 = clock64();
+  while (ld_acquire_sys_u64(flag) < want) {
+    if (clock64() - t0 > 60000000000LL) {  // ~30 s at 2 GHz
+      printf("b200ep: rank %d timed out waiting for flag kind %d from rank %d (want %llu, have %llu)\n", me, what,
+             peer, (unsigned long long)want, (unsigned long long)ld_acquire_sys_u64(flag));
+      __trap();
+    }
+    __nanosleep(20);
+  }
+}
+
+// "All CTAs of this kernel have finished their stores" -> signal every peer.
+// Call with all threads of the CTA after the CTA's last store (and after bulk_wait_all()).
+// counter: private device word, must be 0 before the kernel and is reset to 0 by the last CTA.
+__device__ __forceinline__ void cta_done_then_signal(unsigned* counter, const Peers& peers, int world, int cat, int slot,
+                                                     int me, uint64_t epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    unsigned prev = atomicAdd(counter, 1u);
+    if (prev == gridDim.x - 1) {
+      __threadfence_system();
+      *counter = 0;
+      for (int d = 0; d < world; ++d)
+        st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[d] + flag_off(cat, slot, me)), epoch);
+    }
+  }
+}
+
+// All CTAs wait for every source rank's flag (flags live in MY region).
+__device__ __forceinline__ void cta_wait_all_sources(const char* my_base, int world, int cat, int slot, int me,
+                                                     uint64_t epoch) {
+  if ((int)threadIdx.x < world)
+    wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(cat, slot, threadIdx.x)), epoch, cat, me,
+                  threadIdx.x);
+  __syncthreads();
+}
+
+// ---- FP8 e4m3 quantisation of 8 bf16 values held in an int4 (arithmetic "div", see oracle/fp8.py)
+__device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
+  const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ float absmax8(const float (&f)[8]) {
+  float m = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m = fmaxf(m, fabsf(f[i]));
+  return m;
+}
+__device__ __forceinline__ float group_scale(float amax, bool ue8m0) {
+  float s = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+  if (ue8m0) {  // 2^ceil(log2 s), exact on the bit pattern
+    uint32_t u = __float_as_uint(s);
+    u = (u & 0x7f800000u) + ((u & 0x007fffffu) ? 0x00800000u : 0u);
+    s = __uint_as_float(u);
+  }
+  return s;
+}
+__device__ __forceinline__ uint2 quant8(const float (&f)[8], float s) {
+  uint32_t o[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float2 a = make_float2(__fdiv_rn(f[4 * i], s), __fdiv_rn(f[4 * i + 1], s));
+    float2 b = make_float2(__fdiv_rn(f[4 * i + 2], s), __fdiv_rn(f[4 * i + 3], s));
+    uint32_t lo = __nv_cvt_float2_to_fp8x2(a, __NV_SATFINITE, __NV_E4M3);
+    uint32_t hi = __nv_cvt_float2_to_fp8x2(b, __NV_SATFINITE, __NV_E4M3);
+    o[i] = lo | (hi << 16);
+  }
+  return make_uint2(o[0], o[1]);
+}
+
+#endif  // __CUDACC__
+
+// ------------------------------------------------------------------ host side
+void set_error(const char* fmt, ...);
+#define B200EP_CUDA(call)                                                                        \
+  do {                                                                                           \
+    cudaError_t e_ = (call);                                                                     \
+    if (e_ != cudaSuccess) {                                                                     \
+      b200ep::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      return B200EP_ERR_CUDA;                                                                    \
+    }                                                                                            \
+  } while (0)
+
+}  // namespace b200ep
+
+// Private scratch layout (device memory owned by the context, not peer visible)
+namespace b200ep {
+constexpr int kMaxLayoutBlocks = 1024;
+struct LocalScratch {
+  unsigned done[16];                                         // CTA-completion counters, one per kernel family
+  unsigned long long layout_ticket;                          // monotonically increasing block ticket
+  unsigned long long layout_pub[kMaxLayoutBlocks][kMaxRanks]; // (epoch << 32 | count) per block and rank
+  HtMeta ht[kNumSlots];
+};
+// pinned host mirror of the count exchange result
+struct HostMirror {
+  volatile unsigned long long epoch[kNumSlots];
+  int32_t num_recv[kNumSlots];
+  int32_t rank_prefix[kNumSlots][kMaxRanks + 1];
+  int32_t recv_per_expert[kNumSlots][kMaxLocalExperts];
+};
+}  // namespace b200ep
+
+struct b200ep_ctx {
+  int rank, world, device, num_sms, sm_limit;
+  char* sym;
+  size_t sym_bytes, slot_bytes;
+  b200ep::Peers peers;
+  bool ipc_open[b200ep::kMaxRanks];
+  bool connected;
+  b200ep::LocalScratch* local;   // device
+  char* ll_local;                // device scratch for low-latency tables
+  size_t ll_local_bytes;
+  b200ep::HostMirror* host;      // pinned, mapped
+  b200ep::HostMirror* host_dev;  // device alias of `host`
+  uint64_t epoch[b200ep::kNumFlagCat][b200ep::kNumSlots];
+  uint64_t layout_epoch, layout_ticket_base;
+  b200ep::HtPlan ht_plan[b200ep::kNumSlots];
+  b200ep::LlPlan ll_plan[b200ep::kNumSlots];
+  int ht_e_local[b200ep::kNumSlots];  // E/world of the last notify on the slot
+  int ht_tokens[b200ep::kNumSlots];   // T of the last dispatch on the slot
+};
+
+namespace b200ep {
+inline char* slot_base(const b200ep_ctx* c, const char* base, int slot) {
+  return const_cast<char*>(base) + kCtrlBytes + (size_t)slot * c->slot_bytes;
+}
+int make_ht_plan(const b200ep_ctx* c, int H, int K, int x_kind, HtPlan* p);
+int make_ll_plan(const b200ep_ctx* c, int H, int K, int E, int max_tok, int use_fp8, LlPlan* p);
+}  // namespace b200ep

@@ -1,0 +1,554 @@
+// High-throughput (prefill) dispatch and combine (north-star kernels 2 and 3, HT mode).
+//
+// Replaces deep_ep.Buffer.dispatch / .combine as vLLM calls them
+// (vllm/model_executor/layers/fused_moe/prepare_finalize/deepep_ht.py:139-162,364-376)
+// and folds in the per-token-group FP8 quantisation vLLM runs before the dispatch
+// (deepep_ht.py:282-289 -> quantization/utils/fp8_utils.py:510-591).  CPU
+// restatement: oracle/dispatch.py (ht_dispatch), oracle/combine.py (ht_combine),
+// oracle/fp8.py (formula "div").
+//
+// Data path (no ring buffers, no receiver-side copy):
+//   notify   every rank writes its per-destination and per-expert counts into
+//            every peer's control block and raises a flag; after the wait each
+//            rank knows the whole W x W count matrix, hence the first row it owns
+//            in every destination's receive region (canonical order: source rank
+//            ascending, source token ascending).
+//   dispatch one warp per token: 16-byte loads -> (fp32 amax per 128 group ->
+//            IEEE divide -> e4m3) -> shared memory row -> ONE TMA bulk copy
+//            (cp.async.bulk) per destination rank straight into the peer's receive
+//            region at its final row; top-k ids are rewritten to destination-local
+//            ids on the way.  recv_x is then read in place by the experts.
+//   combine  expert ranks push result rows (bf16) with the same staging + bulk copy
+//            into the source rank's stage [token][dst rank]; the source rank sums
+//            the <= W rows of a token in fp32 in rank order and writes bf16 once.
+// Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> CTA barrier ->
+// fence.sys -> CTA counter -> (last CTA) st.release.sys flag in every peer;
+// consumers spin with ld.acquire.sys.
+#include "common.cuh"
+
+namespace b200ep {
+
+// ------------------------------------------------------------------ notify
+__global__ void __launch_bounds__(256)
+    ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, const int32_t* __restrict__ tok_per_rank,
+                          const int32_t* __restrict__ tok_per_expert, uint64_t epoch) {
+  for (int d = 0; d < W; ++d) {
+    char* ctrl = peers.base[d];
+    int32_t* cr = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntRankOff) + ((size_t)slot * kMaxRanks + me) * kMaxRanks;
+    int32_t* ce = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntExpOff) + ((size_t)slot * kMaxRanks + me) * kMaxLocalExperts;
+    if ((int)threadIdx.x < W) cr[threadIdx.x] = tok_per_rank[threadIdx.x];
+    for (int i = threadIdx.x; i < e_local; i += blockDim.x) ce[i] = tok_per_expert[d * e_local + i];
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < W) {
+    __threadfence_system();
+    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[threadIdx.x] + flag_off(kFlagHtNotify, slot, me)), epoch);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    ht_notify_recv_kernel(const char* my_base, int W, int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
+                          uint64_t epoch) {
+  cta_wait_all_sources(my_base, W, kFlagHtNotify, slot, me, epoch);
+  const int32_t* cr = reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntRankOff) + (size_t)slot * kMaxRanks * kMaxRanks;
+  const int32_t* ce =
+      reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntExpOff) + (size_t)slot * kMaxRanks * kMaxLocalExperts;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    int p = 0;
+    for (int s = 0; s < W; ++s) {
+      meta->rank_prefix[s] = p;
+      host->rank_prefix[slot][s] = p;
+      p += __ldcg(&cr[s * kMaxRanks + me]);
+    }
+    meta->rank_prefix[W] = p;
+    host->rank_prefix[slot][W] = p;
+    meta->num_recv = p;
+    host->num_recv[slot] = p;
+  }
+  if (tid >= 32 && tid < 32 + W) {
+    const int d = tid - 32;
+    int b = 0;
+    for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * kMaxRanks + d]);
+    meta->send_base[d] = b;
+  }
+  for (int i = tid; i < e_local; i += blockDim.x) {
+    int n = 0;
+    for (int s = 0; s < W; ++s) n += __ldcg(&ce[(size_t)s * kMaxLocalExperts + i]);
+    meta->recv_per_expert[i] = n;
+    host->recv_per_expert[slot][i] = n;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence_system();
+    host->epoch[slot] = epoch;
+  }
+}
+
+// ------------------------------------------------------------------ dispatch
+struct HtDispatchArgs {
+  Peers peers;
+  HtPlan plan;
+  const void* x;
+  const float* x_scales;
+  const void* ids;
+  const float* weights;
+  const uint8_t* in_rank;
+  const int32_t* send_off;
+  const HtMeta* meta;
+  unsigned* done;
+  size_t slot_off;  // kCtrlBytes + slot * slot_bytes
+  uint64_t epoch;
+  int T, W, me, slot, e_local, ue8m0, ids_i64;
+};
+
+// Stage one token row in shared memory.  KIND: B200EP_X_* ; returns nothing, all lanes participate.
+template <int KIND>
+__device__ __forceinline__ void stage_row(const HtDispatchArgs& a, int t, char* s_row, float* s_scale, int lane) {
+  const int H = a.plan.H;
+  if (KIND == B200EP_X_BF16_QUANT) {
+    // 16 lanes x 8 bf16 = one 128-element group; a warp covers two groups per step.
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
+    const int nvec = H / 8;
+    constexpr int U = 4;
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      int4 raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        raw[u] = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        float f[8];
+        unpack8(raw[u], f);
+        float m = absmax8(f);
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        const float s = group_scale(m, a.ue8m0 != 0);
+        if (v < nvec) {
+          *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
+          if ((lane & 15) == 0) s_scale[v >> 4] = s;
+        }
+      }
+    }
+  } else {
+    const int row_bytes = a.plan.row_bytes;
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * row_bytes);
+    const int nvec = row_bytes / 16;
+    constexpr int U = 4;
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      int4 raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) raw[u] = ld_nc_v4(src + v);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
+      }
+    }
+    if (KIND == B200EP_X_FP8) {
+      const int ng = H / kGroup;
+      for (int g = lane; g < ng; g += 32) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+    }
+  }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(512) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int W = a.W, K = a.plan.K;
+  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
+  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
+  char* s_row = s_mem + (size_t)warp * stage_bytes;
+  float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+
+  for (int t = blockIdx.x * nwarp + warp; t < a.T; t += gridDim.x * nwarp) {
+    // destination set of this token: lane d holds rank d's membership and row
+    int my_in = 0, my_row = -1;
+    if (lane < W) {
+      my_in = a.in_rank[(size_t)t * W + lane];
+      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
+    }
+    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
+    if (dmask == 0) continue;
+
+    bulk_wait_read0();  // my previous bulk copies have finished reading the stage
+    __syncwarp();
+    stage_row<KIND>(a, t, s_row, s_scale, lane);
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (my_in) {
+      char* dst = a.peers.base[lane] + a.slot_off;
+      bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
+      if (scale_bytes) {
+        if ((scale_bytes & 15) == 0) {
+          bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
+        }
+      }
+      bulk_commit();
+      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+    }
+    if (scale_bytes && (scale_bytes & 15)) {  // rows whose scale vector is not a 16-byte multiple: plain stores
+      const int ng = scale_bytes / 4;
+      for (int d = 0; d < W; ++d) {
+        if (!((dmask >> d) & 1u)) continue;
+        const int row = __shfl_sync(0xffffffffu, my_row, d);
+        float* dsts = reinterpret_cast<float*>(a.peers.base[d] + a.slot_off + a.plan.off_scales + (size_t)row * scale_bytes);
+        for (int g = lane; g < ng; g += 32) dsts[g] = s_scale[g];
+      }
+    }
+    // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
+    long long id = -1;
+    float w = 0.f;
+    if (lane < K) {
+      id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
+                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
+      w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+    }
+    const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
+    for (int d = 0; d < W; ++d) {
+      if (!((dmask >> d) & 1u)) continue;
+      const int row = __shfl_sync(0xffffffffu, my_row, d);
+      if (lane < K) {
+        char* dst = a.peers.base[d] + a.slot_off;
+        const bool mine = owner == d;
+        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
+        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
+      }
+    }
+  }
+  bulk_wait_all();
+  cta_done_then_signal(a.done, a.peers, W, kFlagHtData, a.slot, a.me, a.epoch);
+}
+
+__global__ void wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me, uint64_t epoch) {
+  cta_wait_all_sources(my_base, W, cat, slot, me, epoch);
+}
+
+// ------------------------------------------------------------------ combine
+struct HtCombineArgs {
+  Peers peers;
+  HtPlan plan;
+  const void* y;    // bf16 [M, H]
+  void* out;        // bf16 [T, H]
+  const uint8_t* in_rank;
+  const int32_t* send_off;
+  const HtMeta* meta;
+  unsigned* done;
+  size_t slot_off;
+  uint64_t epoch;
+  int T, W, me, slot;
+};
+
+// Expert rank: result row m goes back to (source rank, source token) = stage[t][me] on that rank.
+// Rows whose source is this rank are left where they are; the reduce reads dev_y directly.
+__global__ void __launch_bounds__(512) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int W = a.W;
+  const int row_bytes = 2 * a.plan.H;
+  char* s_row = s_mem + (size_t)warp * row_bytes;
+  const int M = a.meta->num_recv;
+  const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  const int nvec = row_bytes / 16;
+
+  for (int m = blockIdx.x * nwarp + warp; m < M; m += gridDim.x * nwarp) {
+    int s = 0;
+    while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
+    if (s == a.me) continue;
+    const int t = __ldcg(src_idx + m);
+    bulk_wait_read0();
+    __syncwarp();
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
+    constexpr int U = 4;
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      int4 raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) raw[u] = ld_nc_v4(src + v);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      char* dst = a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes;
+      bulk_s2g(dst, s_row, row_bytes);
+      bulk_commit();
+    }
+  }
+  bulk_wait_all();
+  cta_done_then_signal(a.done, a.peers, W, kFlagHtComb, a.slot, a.me, a.epoch);
+}
+
+__device__ __forceinline__ void acc8(float (&acc)[8], const int4& v) {
+  float f[8];
+  unpack8(v, f);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], f[i]);
+}
+__device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 p = __floats2bfloat162_rn(acc[2 * i], acc[2 * i + 1]);
+    o[i] = *reinterpret_cast<uint32_t*>(&p);
+  }
+  return make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]);
+}
+
+// Source rank: out[t] = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ).
+__global__ void __launch_bounds__(512) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
+  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int W = a.W;
+  const int row_bytes = 2 * a.plan.H;
+  const int nvec = row_bytes / 16;
+  const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
+  const int my_first = a.meta->rank_prefix[a.me];
+
+  for (int t = blockIdx.x * nwarp + warp; t < a.T; t += gridDim.x * nwarp) {
+    const char* rowp = nullptr;
+    if (lane < W && a.in_rank[(size_t)t * W + lane]) {
+      rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + a.send_off[(size_t)t * W + lane]) * row_bytes
+                          : stage + ((size_t)t * W + lane) * row_bytes;
+    }
+    const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
+    const char* rows[kMaxRanks];
+#pragma unroll
+    for (int d = 0; d < kMaxRanks; ++d)
+      rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
+    int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
+    for (int v = lane; v < nvec; v += 32) {
+      int4 raw[kMaxRanks];
+#pragma unroll
+      for (int d = 0; d < kMaxRanks; ++d)
+        if ((dmask >> d) & 1u) raw[d] = ld_cg_v4(rows[d] + (size_t)v * 16);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int d = 0; d < kMaxRanks; ++d)
+        if ((dmask >> d) & 1u) acc8(acc, raw[d]);
+      st_na_v4(dst + v, pack8_bf16(acc));
+    }
+  }
+}
+
+static int grid_for(const b200ep_ctx* c, int items, int per_cta, int ctas_per_sm) {
+  int sms = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
+  int g = (items + per_cta - 1) / per_cta;
+  int cap = sms * ctas_per_sm;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return g;
+}
+
+}  // namespace b200ep
+
+using namespace b200ep;
+
+static int check_slot(b200ep_ctx* c, int slot, const char* who) {
+  if (!c || slot < 0 || slot >= kNumSlots) {
+    set_error("%s: bad context or slot", who);
+    return B200EP_ERR_ARG;
+  }
+  if (!c->connected) {
+    set_error("%s: peers not connected (call b200ep_import_handles / b200ep_set_peer_ptrs first)", who);
+    return B200EP_ERR_STATE;
+  }
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_tokens_per_rank,
+                                const int32_t* dev_tokens_per_expert, int E, int phases, void* stream) {
+  int rc = check_slot(c, slot, "ht_notify");
+  if (rc) return rc;
+  if (E <= 0 || E % c->world || E / c->world > kMaxLocalExperts) {
+    set_error("ht_notify: bad E=%d for world=%d", E, c->world);
+    return B200EP_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  const int el = E / c->world;
+  if (phases & B200EP_PHASE_SEND) {
+    if (!dev_tokens_per_rank || !dev_tokens_per_expert) {
+      set_error("ht_notify: null counts");
+      return B200EP_ERR_ARG;
+    }
+    const uint64_t ep = ++c->epoch[kFlagHtNotify][slot];
+    c->ht_e_local[slot] = el;
+    ht_notify_send_kernel<<<1, 256, 0, st>>>(c->peers, c->world, c->rank, slot, el, dev_tokens_per_rank,
+                                             dev_tokens_per_expert, ep);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  if (phases & B200EP_PHASE_RECV) {
+    ht_notify_recv_kernel<<<1, 256, 0, st>>>(c->sym, c->world, c->rank, slot, el, &c->local->ht[slot], c->host_dev,
+                                             c->epoch[kFlagHtNotify][slot]);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
+                                  int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
+                                  const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H, int K,
+                                  int E, int phases, void* stream) {
+  int rc = check_slot(c, slot, "ht_dispatch");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  if (phases & B200EP_PHASE_SEND) {
+    HtPlan plan;
+    rc = make_ht_plan(c, H, K, x_kind, &plan);
+    if (rc) return rc;
+    if (T < 0 || T > plan.t_cap) {
+      set_error("ht_dispatch: T=%d exceeds slot capacity %d tokens/rank (H=%d K=%d kind=%d, region %zu bytes)", T,
+                plan.t_cap, H, K, x_kind, c->sym_bytes);
+      return B200EP_ERR_CAPACITY;
+    }
+    if (E <= 0 || E % c->world) {
+      set_error("ht_dispatch: bad E=%d", E);
+      return B200EP_ERR_ARG;
+    }
+    if (plan.row_bytes % 16) {
+      set_error("ht_dispatch: row of %d bytes is not a multiple of 16", plan.row_bytes);
+      return B200EP_ERR_ARG;
+    }
+    if (T > 0 && (!dev_x || !dev_topk_ids || !dev_is_token_in_rank || !dev_send_off ||
+                  (x_kind == B200EP_X_FP8 && !dev_x_scales))) {
+      set_error("ht_dispatch: null pointer");
+      return B200EP_ERR_ARG;
+    }
+    c->ht_plan[slot] = plan;
+    c->ht_tokens[slot] = T;
+    HtDispatchArgs a;
+    a.peers = c->peers;
+    a.plan = plan;
+    a.x = dev_x;
+    a.x_scales = dev_x_scales;
+    a.ids = dev_topk_ids;
+    a.weights = dev_topk_weights;
+    a.in_rank = dev_is_token_in_rank;
+    a.send_off = dev_send_off;
+    a.meta = &c->local->ht[slot];
+    a.done = &c->local->done[0 + slot];
+    a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
+    a.epoch = ++c->epoch[kFlagHtData][slot];
+    a.T = T;
+    a.W = c->world;
+    a.me = c->rank;
+    a.slot = slot;
+    a.e_local = E / c->world;
+    a.ue8m0 = ue8m0;
+    a.ids_i64 = ids_i64;
+    const int stage_bytes = (plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    int warps = 100 * 1024 / stage_bytes;  // two CTAs per SM
+    if (warps > 12) warps = 12;
+    if (warps < 1) warps = 1;
+    const size_t smem = (size_t)warps * stage_bytes;
+    const int grid = grid_for(c, T, warps, 2);
+    auto launch = [&](auto kern) -> int {
+      B200EP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern<<<grid, warps * 32, smem, st>>>(a);
+      B200EP_CUDA(cudaGetLastError());
+      return B200EP_OK;
+    };
+    if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>);
+    else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>);
+    else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>);
+    if (rc) return rc;
+  }
+  if (phases & B200EP_PHASE_RECV) {
+    wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, c->epoch[kFlagHtData][slot]);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ht_views(b200ep_ctx* c, int slot, b200ep_ht_view* out) {
+  if (!c || !out || slot < 0 || slot >= kNumSlots) {
+    set_error("ht_views: bad argument");
+    return B200EP_ERR_ARG;
+  }
+  const HtPlan& p = c->ht_plan[slot];
+  if (p.H == 0) {
+    set_error("ht_views: no dispatch has run on slot %d", slot);
+    return B200EP_ERR_STATE;
+  }
+  char* b = slot_base(c, c->sym, slot);
+  out->recv_x = b + p.off_x;
+  out->recv_x_scales = p.scale_bytes ? reinterpret_cast<float*>(b + p.off_scales) : nullptr;
+  out->recv_topk_idx = reinterpret_cast<int64_t*>(b + p.off_idx);
+  out->recv_topk_weights = reinterpret_cast<float*>(b + p.off_w);
+  out->recv_src_idx = reinterpret_cast<int32_t*>(b + p.off_src);
+  out->rank_prefix = c->local->ht[slot].rank_prefix;
+  out->recv_per_expert = c->local->ht[slot].recv_per_expert;
+  out->capacity_rows = p.cap_rows;
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, void* dev_out,
+                                 const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H,
+                                 int phases, void* stream) {
+  int rc = check_slot(c, slot, "ht_combine");
+  if (rc) return rc;
+  const HtPlan& plan = c->ht_plan[slot];
+  if (plan.H == 0 || plan.H != H || T != c->ht_tokens[slot]) {
+    set_error("ht_combine: no matching dispatch on slot %d (H=%d/%d, T=%d/%d)", slot, H, plan.H, T, c->ht_tokens[slot]);
+    return B200EP_ERR_STATE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  HtCombineArgs a;
+  a.peers = c->peers;
+  a.plan = plan;
+  a.y = dev_y;
+  a.out = dev_out;
+  a.in_rank = dev_is_token_in_rank;
+  a.send_off = dev_send_off;
+  a.meta = &c->local->ht[slot];
+  a.done = &c->local->done[2 + slot];
+  a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
+  a.T = T;
+  a.W = c->world;
+  a.me = c->rank;
+  a.slot = slot;
+  const int row_bytes = 2 * H;
+  if (phases & B200EP_PHASE_SEND) {
+    a.epoch = ++c->epoch[kFlagHtComb][slot];
+    int warps = 200 * 1024 / row_bytes;
+    if (warps > 16) warps = 16;
+    if (warps < 1) warps = 1;
+    const size_t smem = (size_t)warps * row_bytes;
+    // M lives on the device; size the grid for the worst case the host knows (mirror of the last notify)
+    const int M = c->host->num_recv[slot];
+    const int grid = grid_for(c, M, warps, 1);
+    B200EP_CUDA(cudaFuncSetAttribute(ht_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ht_combine_send_kernel<<<grid, warps * 32, smem, st>>>(a);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  if (phases & B200EP_PHASE_RECV) {
+    if (T > 0 && (!dev_out || !dev_is_token_in_rank || !dev_send_off)) {
+      set_error("ht_combine: null pointer");
+      return B200EP_ERR_ARG;
+    }
+    a.epoch = c->epoch[kFlagHtComb][slot];
+    const int warps = 16;
+    const int grid = grid_for(c, T, warps, 2);
+    ht_combine_recv_kernel<<<grid, warps * 32, 0, st>>>(a);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  return B200EP_OK;
+}

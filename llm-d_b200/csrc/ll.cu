@@ -1,0 +1,477 @@
+// Low-latency (decode) dispatch and combine (north-star kernels 2 and 3, LL mode).
+//
+// Replaces deep_ep.Buffer.low_latency_dispatch / low_latency_combine as vLLM calls
+// them (vllm/model_executor/layers/fused_moe/prepare_finalize/deepep_ll.py:292-314,
+// 399-408).  Output layout = BatchedExperts, the one
+// prepare_finalize/batched.py:82-152 builds: packed_recv_x[e_local, slot, :] with
+// the tokens of an expert packed at slots [0, count).  CPU restatement:
+// oracle/dispatch.py (ll_dispatch), oracle/combine.py (ll_combine).
+//
+// No host synchronisation, fixed shapes, no allocation, counters keyed by a call
+// epoch instead of being reset: the launches replay unchanged under a CUDA graph.
+//
+// Order is canonical (source rank ascending, source token ascending) and needs no
+// atomics: every rank first publishes its per-expert counts to all peers (1 KB each),
+// so a sender can compute the final slot of each of its (token, expert) rows,
+//     slot = sum_{s < me} count[s][e] + (position of the token among my tokens for e),
+// and writes the row ONCE, straight to that slot on the owner (no receive-side pack).
+//   COUNT  one CTA: ballot/popc positions per expert, counts -> peers, flag.
+//   SEND   one CTA per token: quantise into shared memory while the counts are in
+//          flight, wait for the count flags, then K TMA bulk copies (cp.async.bulk)
+//          smem -> peer; last CTA raises the data flags.
+//   RECV   wait for the data flags (DeepEP's "recv hook").
+// Combine: owners push occupied result rows back into stage[token][k] on the source
+// (same staging + bulk copy); the source does sum_k w_k * y_k in fp32 (multiply, then
+// add, k ascending) and writes bf16 once.
+#include "common.cuh"
+
+namespace b200ep {
+
+constexpr int kLlMaxExperts = kMaxLocalExperts;  // global experts in LL mode (count row of the control block)
+constexpr int kLlMaxTokens = 1024;
+
+struct LlScratch {  // private, per slot
+  int32_t cnt_mine[kLlMaxExperts];
+  int32_t pos[kLlMaxTokens * kMaxTopk];
+  int32_t send_slot[kLlMaxTokens * kMaxTopk];
+  int32_t recv_count[kMaxLocalExperts];
+  int32_t layout_range[kMaxLocalExperts * kMaxRanks * 2];
+};
+static_assert(sizeof(LlScratch) * kNumSlots <= (4u << 20), "ll scratch");
+
+template <typename IdT>
+__global__ void __launch_bounds__(1024)
+    ll_count_kernel(Peers peers, int W, int me, int slot, const IdT* __restrict__ ids, int T, int K, int E,
+                    LlScratch* sc, uint64_t epoch) {
+  extern __shared__ int s_ids[];  // transposed [K][Tp] so that lanes read consecutive words
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const int Tp = (T + 31) / 32 * 32;
+  for (int i = tid; i < K * Tp; i += blockDim.x) {
+    const int k = i / Tp, t = i % Tp;
+    long long v = t < T ? (long long)ids[(size_t)t * K + k] : -1;
+    s_ids[i] = (v >= 0 && v < E) ? (int)v : -1;
+  }
+  __syncthreads();
+  for (int e = warp; e < E; e += nwarp) {
+    int base = 0;
+    for (int c = 0; c < Tp; c += 32) {
+      const int t = c + lane;
+      int hit = -1;
+      for (int k = 0; k < K; ++k)
+        if (s_ids[k * Tp + t] == e) hit = k;
+      const unsigned ball = __ballot_sync(0xffffffffu, hit >= 0);
+      if (hit >= 0) sc->pos[t * K + hit] = base + __popc(ball & ((1u << lane) - 1u));
+      base += __popc(ball);
+    }
+    if (lane == 0) sc->cnt_mine[e] = base;
+  }
+  __syncthreads();
+  for (int d = 0; d < W; ++d) {
+    int32_t* ce = reinterpret_cast<int32_t*>(peers.base[d] + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + me) * kLlMaxExperts;
+    for (int i = tid; i < E; i += blockDim.x) ce[i] = sc->cnt_mine[i];
+  }
+  __syncthreads();
+  if (tid < W) {
+    __threadfence_system();
+    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[tid] + flag_off(kFlagLlCount, slot, me)), epoch);
+  }
+}
+
+struct LlDispatchArgs {
+  Peers peers;
+  LlPlan plan;
+  const __nv_bfloat16* x;
+  const void* ids;
+  LlScratch* sc;
+  unsigned* done;
+  size_t slot_off;
+  uint64_t epoch_cnt, epoch_data;
+  int T, W, me, slot, E, ue8m0, ids_i64;
+};
+
+template <bool kFp8>
+__global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_constant__ LlDispatchArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int W = a.W, K = a.plan.K, H = a.plan.H, e_local = a.plan.e_local, cap = a.plan.cap;
+  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
+  char* s_row = s_mem;
+  float* s_scale = reinterpret_cast<float*>(s_mem + row_bytes);
+  const char* my_base = a.peers.base[a.me];
+  const int32_t* cnt = reinterpret_cast<const int32_t*>(my_base + kCtrlLlCntOff) + (size_t)a.slot * kMaxRanks * kLlMaxExperts;
+  bool counts_ready = false;
+
+  for (int t = blockIdx.x; t < a.T || !counts_ready; t += gridDim.x) {
+    const bool have_token = t < a.T;
+    if (have_token) {
+      if (tid < K) bulk_wait_read0();  // issuing threads: previous copies have read the stage
+      __syncthreads();
+      const int4* src = reinterpret_cast<const int4*>(a.x + (size_t)t * H);
+      const int nvec = H / 8;
+      if (kFp8) {
+        for (int v0 = 0; v0 < nvec; v0 += 256) {
+          const int v = v0 + tid;
+          int4 raw = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
+          float f[8];
+          unpack8(raw, f);
+          float m = absmax8(f);
+          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+          const float s = group_scale(m, a.ue8m0 != 0);
+          if (v < nvec) {
+            *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
+            if ((lane & 15) == 0) s_scale[v >> 4] = s;
+          }
+        }
+      } else {
+        for (int v = tid; v < nvec; v += 256) reinterpret_cast<int4*>(s_row)[v] = ld_nc_v4(src + v);
+      }
+      fence_proxy_async_smem();
+    }
+    if (!counts_ready) {
+      cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt);
+      counts_ready = true;
+      if (blockIdx.x == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
+        for (int el = tid; el < e_local; el += blockDim.x) {
+          int p = 0;
+          for (int s = 0; s < W; ++s) {
+            const int n = __ldcg(&cnt[(size_t)s * kLlMaxExperts + a.me * e_local + el]);
+            a.sc->layout_range[(el * W + s) * 2] = p;
+            a.sc->layout_range[(el * W + s) * 2 + 1] = n;
+            p += n;
+          }
+          a.sc->recv_count[el] = p;
+        }
+      }
+    }
+    __syncthreads();
+    if (have_token && tid < K) {
+      const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + tid]
+                                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + tid];
+      int slot_idx = -1;
+      if (id >= 0 && id < a.E) {
+        const int e = (int)id, d = e / e_local, el = e % e_local;
+        int base = 0;
+        for (int s = 0; s < a.me; ++s) base += __ldcg(&cnt[(size_t)s * kLlMaxExperts + e]);
+        slot_idx = base + a.sc->pos[t * K + tid];
+        if (slot_idx < cap) {
+          char* dst = a.peers.base[d] + a.slot_off;
+          const size_t r = (size_t)el * cap + slot_idx;
+          bulk_s2g(dst + a.plan.off_x + r * row_bytes, s_row, row_bytes);
+          if (kFp8 && (scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + r * scale_bytes, s_scale, scale_bytes);
+          bulk_commit();
+          if (kFp8 && (scale_bytes & 15)) {
+            float* ds = reinterpret_cast<float*>(dst + a.plan.off_scales + r * scale_bytes);
+            for (int g = 0; g < scale_bytes / 4; ++g) ds[g] = s_scale[g];
+          }
+          *reinterpret_cast<int32_t*>(dst + a.plan.off_src + r * 4) = t * K + tid;
+        } else {
+          printf("b200ep: rank %d ll_dispatch overflow: expert %d slot %d >= capacity %d\n", a.me, e, slot_idx, cap);
+          __trap();
+        }
+      }
+      a.sc->send_slot[t * K + tid] = slot_idx;
+    }
+  }
+  if (tid < K) bulk_wait_all();
+  cta_done_then_signal(a.done, a.peers, W, kFlagLlData, a.slot, a.me, a.epoch_data);
+}
+
+struct LlCombineArgs {
+  Peers peers;
+  LlPlan plan;
+  const void* y;  // bf16 [e_local, cap, H]
+  void* out;      // bf16 [T, H]
+  const void* ids;
+  const float* weights;
+  const LlScratch* sc;
+  unsigned* done;
+  size_t slot_off;
+  uint64_t epoch;
+  int T, W, me, slot, E, ids_i64;
+};
+
+__global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_constant__ LlCombineArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int W = a.W, K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
+  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
+  char* s_row = s_mem + (size_t)warp * row_bytes;
+  const int32_t* src_info = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  const int total = e_local * cap;
+  for (int idx = blockIdx.x * nwarp + warp; idx < total; idx += gridDim.x * nwarp) {
+    const int el = idx / cap, sl = idx % cap;
+    if (sl >= a.sc->recv_count[el]) continue;
+    int s = 0;
+    while (s + 1 < W && sl >= a.sc->layout_range[(el * W + s + 1) * 2]) ++s;
+    if (s == a.me) continue;  // the reduce reads local rows straight from dev_y
+    const int flat = __ldcg(src_info + idx);  // t*K + k on the source rank
+    bulk_wait_read0();
+    __syncwarp();
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)idx * row_bytes);
+    constexpr int U = 4;
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      int4 raw[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) raw[u] = ld_nc_v4(src + v);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + (size_t)flat * row_bytes, s_row, row_bytes);
+      bulk_commit();
+    }
+    (void)K;
+  }
+  bulk_wait_all();
+  cta_done_then_signal(a.done, a.peers, W, kFlagLlComb, a.slot, a.me, a.epoch);
+}
+
+// out[t] = bf16( sum_k w[t,k] * row(t,k) ): fp32 multiply, fp32 add, k ascending.
+// A warp owns (token, 512-byte column block) so that 128 tokens still fill the GPU.
+__global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_constant__ LlCombineArgs a) {
+  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
+  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
+  const int nblk = (nvec + 31) / 32;
+  const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
+  const int items = a.T * nblk;
+  for (int it = blockIdx.x * nwarp + warp; it < items; it += gridDim.x * nwarp) {
+    const int t = it / nblk, v = (it % nblk) * 32 + lane;
+    const char* rowp = nullptr;
+    float w = 0.f;
+    if (lane < K) {
+      const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
+                                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
+      if (id >= 0 && id < a.E) {
+        const int e = (int)id;
+        w = a.weights[(size_t)t * K + lane];
+        if (e / e_local == a.me)
+          rowp = reinterpret_cast<const char*>(a.y) + ((size_t)(e % e_local) * cap + a.sc->send_slot[t * K + lane]) * row_bytes;
+        else
+          rowp = stage + ((size_t)t * K + lane) * row_bytes;
+      }
+    }
+    const unsigned kmask = __ballot_sync(0xffffffffu, rowp != nullptr);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k0 = 0; k0 < K; k0 += 8) {
+      int4 raw[8];
+      float wk[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = k0 + j;
+        const char* rp = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, k & 31));
+        wk[j] = __shfl_sync(0xffffffffu, w, k & 31);
+        if (k < K && ((kmask >> k) & 1u) && v < nvec) raw[j] = ld_cg_v4(rp + (size_t)v * 16);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = k0 + j;
+        if (k < K && ((kmask >> k) & 1u)) {
+          float f[8];
+          unpack8(raw[j], f);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = __fadd_rn(acc[i], __fmul_rn(wk[j], f[i]));
+        }
+      }
+    }
+    if (v < nvec) {
+      uint32_t o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        __nv_bfloat162 p = __floats2bfloat162_rn(acc[2 * i], acc[2 * i + 1]);
+        o[i] = *reinterpret_cast<uint32_t*>(&p);
+      }
+      st_na_v4(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes + (size_t)v * 16,
+               make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]));
+    }
+  }
+}
+
+__global__ void ll_wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me, uint64_t epoch) {
+  cta_wait_all_sources(my_base, W, cat, slot, me, epoch);
+}
+
+}  // namespace b200ep
+
+using namespace b200ep;
+
+static int ll_check(b200ep_ctx* c, int slot, const char* who) {
+  if (!c || slot < 0 || slot >= kNumSlots) {
+    set_error("%s: bad context or slot", who);
+    return B200EP_ERR_ARG;
+  }
+  if (!c->connected) {
+    set_error("%s: peers not connected", who);
+    return B200EP_ERR_STATE;
+  }
+  return B200EP_OK;
+}
+
+static int ll_grid(const b200ep_ctx* c, int want) {
+  int sms = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
+  if (want > sms) want = sms;
+  return want < 1 ? 1 : want;
+}
+
+extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf16, const void* dev_topk_ids,
+                                  int ids_i64, int T, int H, int K, int E, int max_tokens_per_rank, int use_fp8,
+                                  int ue8m0, int phases, void* stream) {
+  int rc = ll_check(c, slot, "ll_dispatch");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  LlPlan plan;
+  rc = make_ll_plan(c, H, K, E, max_tokens_per_rank, use_fp8, &plan);
+  if (rc) return rc;
+  if (T < 0 || T > max_tokens_per_rank || T > kLlMaxTokens || E > kLlMaxExperts) {
+    set_error("ll_dispatch: T=%d must be <= max_tokens_per_rank=%d (<= %d), E=%d <= %d", T, max_tokens_per_rank,
+              kLlMaxTokens, E, kLlMaxExperts);
+    return B200EP_ERR_ARG;
+  }
+  if (T > 0 && (!dev_x_bf16 || !dev_topk_ids)) {
+    set_error("ll_dispatch: null pointer");
+    return B200EP_ERR_ARG;
+  }
+  LlScratch* sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
+  if (phases & B200EP_LL_PHASE_COUNT) {
+    c->ll_plan[slot] = plan;
+    const uint64_t ep = ++c->epoch[kFlagLlCount][slot];
+    const int Tp = (T + 31) / 32 * 32;
+    const size_t smem = (size_t)K * Tp * 4;
+    if (ids_i64) {
+      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      ll_count_kernel<int64_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int64_t*)dev_topk_ids,
+                                                     T, K, E, sc, ep);
+    } else {
+      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      ll_count_kernel<int32_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int32_t*)dev_topk_ids,
+                                                     T, K, E, sc, ep);
+    }
+    B200EP_CUDA(cudaGetLastError());
+  }
+  if (phases & B200EP_LL_PHASE_SEND) {
+    LlDispatchArgs a;
+    a.peers = c->peers;
+    a.plan = plan;
+    a.x = (const __nv_bfloat16*)dev_x_bf16;
+    a.ids = dev_topk_ids;
+    a.sc = sc;
+    a.done = &c->local->done[4 + slot];
+    a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
+    a.epoch_cnt = c->epoch[kFlagLlCount][slot];
+    a.epoch_data = ++c->epoch[kFlagLlData][slot];
+    a.T = T;
+    a.W = c->world;
+    a.me = c->rank;
+    a.slot = slot;
+    a.E = E;
+    a.ue8m0 = ue8m0;
+    a.ids_i64 = ids_i64;
+    const size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    const int grid = ll_grid(c, T);
+    if (use_fp8) {
+      B200EP_CUDA(cudaFuncSetAttribute(ll_dispatch_send_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      ll_dispatch_send_kernel<true><<<grid, 256, smem, st>>>(a);
+    } else {
+      B200EP_CUDA(cudaFuncSetAttribute(ll_dispatch_send_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      ll_dispatch_send_kernel<false><<<grid, 256, smem, st>>>(a);
+    }
+    B200EP_CUDA(cudaGetLastError());
+  }
+  if (phases & B200EP_LL_PHASE_RECV) {
+    ll_wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagLlData, slot, c->rank, c->epoch[kFlagLlData][slot]);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ll_views(b200ep_ctx* c, int slot, b200ep_ll_view* out) {
+  if (!c || !out || slot < 0 || slot >= kNumSlots) {
+    set_error("ll_views: bad argument");
+    return B200EP_ERR_ARG;
+  }
+  const LlPlan& p = c->ll_plan[slot];
+  if (p.H == 0) {
+    set_error("ll_views: no low-latency dispatch has run on slot %d", slot);
+    return B200EP_ERR_STATE;
+  }
+  char* b = slot_base(c, c->sym, slot);
+  LlScratch* sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
+  out->packed_recv_x = b + p.off_x;
+  out->packed_recv_scales = p.scale_bytes ? reinterpret_cast<float*>(b + p.off_scales) : nullptr;
+  out->recv_count = sc->recv_count;
+  out->src_info = reinterpret_cast<int32_t*>(b + p.off_src);
+  out->layout_range = sc->layout_range;
+  return B200EP_OK;
+}
+
+extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, const void* dev_topk_ids, int ids_i64,
+                                 const float* dev_topk_weights, void* dev_out, int T, int H, int K, int E,
+                                 int max_tokens_per_rank, int phases, void* stream) {
+  int rc = ll_check(c, slot, "ll_combine");
+  if (rc) return rc;
+  const LlPlan& plan = c->ll_plan[slot];
+  if (plan.H != H || plan.K != K || plan.max_tok != max_tokens_per_rank || plan.e_local != E / c->world) {
+    set_error("ll_combine: no matching low-latency dispatch on slot %d", slot);
+    return B200EP_ERR_STATE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  LlCombineArgs a;
+  a.peers = c->peers;
+  a.plan = plan;
+  a.y = dev_y;
+  a.out = dev_out;
+  a.ids = dev_topk_ids;
+  a.weights = dev_topk_weights;
+  a.sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
+  a.done = &c->local->done[6 + slot];
+  a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
+  a.T = T;
+  a.W = c->world;
+  a.me = c->rank;
+  a.slot = slot;
+  a.E = E;
+  a.ids_i64 = ids_i64;
+  const int row_bytes = 2 * H;
+  if (phases & B200EP_PHASE_SEND) {
+    if (!dev_y) {
+      set_error("ll_combine: null dev_y");
+      return B200EP_ERR_ARG;
+    }
+    a.epoch = ++c->epoch[kFlagLlComb][slot];
+    int warps = 200 * 1024 / row_bytes;
+    if (warps > 16) warps = 16;
+    if (warps < 1) warps = 1;
+    const size_t smem = (size_t)warps * row_bytes;
+    const int grid = ll_grid(c, c->num_sms);
+    B200EP_CUDA(cudaFuncSetAttribute(ll_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ll_combine_send_kernel<<<grid, warps * 32, smem, st>>>(a);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  if (phases & B200EP_PHASE_RECV) {
+    if (T > 0 && (!dev_out || !dev_topk_ids || !dev_topk_weights)) {
+      set_error("ll_combine: null pointer");
+      return B200EP_ERR_ARG;
+    }
+    a.epoch = c->epoch[kFlagLlComb][slot];
+    const int nblk = (row_bytes / 16 + 31) / 32;
+    int grid = (T * nblk + 7) / 8;
+    grid = ll_grid(c, grid) * (grid > c->num_sms ? 2 : 1);
+    ll_combine_recv_kernel<<<grid, 256, 0, st>>>(a);
+    B200EP_CUDA(cudaGetLastError());
+  }
+  return B200EP_OK;
+}

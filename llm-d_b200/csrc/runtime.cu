@@ -1,0 +1,297 @@
+// Context, symmetric region, CUDA-IPC bootstrap and region planning for libb200ep.
+//
+// Replaces the runtime half of DeepEP's deep_ep_cpp.Buffer (buffer allocation,
+// IPC handle exchange, destroy) that vLLM drives from
+// vllm/distributed/device_communicators/all2all.py:190-194,222-245,297-315.
+// No NVSHMEM: one cudaMalloc'd region per rank, mapped into every peer with
+// cudaIpcOpenMemHandle; all later traffic is SM-issued stores over NVLink.
+#include <stdarg.h>
+#include <string.h>
+
+#include <atomic>
+#include <chrono>
+#include <new>
+#include <thread>
+
+#include "common.cuh"
+
+namespace b200ep {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// One slot of the high-throughput mode:
+//   receive side  (written by peers' dispatch): x rows, scales, top-k ids, top-k weights, source index
+//   combine stage (written by peers' combine) : [t_cap][world] bf16 rows
+// sized for the worst case (every token of every rank lands here).
+int make_ht_plan(const b200ep_ctx* c, int H, int K, int x_kind, HtPlan* p) {
+  if (H <= 0 || H % kGroup != 0 || K <= 0 || K > kMaxTopk) {
+    set_error("ht: unsupported shape H=%d (must be a positive multiple of 128) K=%d (1..%d)", H, K, kMaxTopk);
+    return B200EP_ERR_ARG;
+  }
+  if (x_kind < B200EP_X_BF16 || x_kind > B200EP_X_FP8) {
+    set_error("ht: bad x_kind %d", x_kind);
+    return B200EP_ERR_ARG;
+  }
+  const int W = c->world;
+  p->H = H;
+  p->K = K;
+  p->x_kind = x_kind;
+  p->row_bytes = x_kind == B200EP_X_BF16 ? 2 * H : H;
+  p->scale_bytes = x_kind == B200EP_X_BF16 ? 0 : H / kGroup * 4;
+  const size_t per_recv_row = (size_t)p->row_bytes + p->scale_bytes + (size_t)K * 12 + 4;
+  const size_t per_token = (size_t)W * per_recv_row + (size_t)W * 2 * H;
+  const size_t slack = 8 * 4096;
+  if (c->slot_bytes <= slack) {
+    set_error("ht: symmetric region too small");
+    return B200EP_ERR_CAPACITY;
+  }
+  long long t_cap = (long long)((c->slot_bytes - slack) / per_token);
+  t_cap = t_cap / 8 * 8;
+  if (t_cap > (1 << 20)) t_cap = 1 << 20;
+  p->t_cap = (int)t_cap;
+  p->cap_rows = W * p->t_cap;
+  size_t off = 0;
+  p->off_x = off;
+  off = align_up(off + (size_t)p->cap_rows * p->row_bytes, 4096);
+  p->off_scales = off;
+  off = align_up(off + (size_t)p->cap_rows * p->scale_bytes, 4096);
+  p->off_idx = off;
+  off = align_up(off + (size_t)p->cap_rows * K * 8, 4096);
+  p->off_w = off;
+  off = align_up(off + (size_t)p->cap_rows * K * 4, 4096);
+  p->off_src = off;
+  off = align_up(off + (size_t)p->cap_rows * 4, 4096);
+  p->off_stage = off;
+  off = align_up(off + (size_t)p->t_cap * W * 2 * H, 4096);
+  if (off > c->slot_bytes) {
+    set_error("ht: internal planning error (%zu > %zu)", off, c->slot_bytes);
+    return B200EP_ERR_CAPACITY;
+  }
+  return B200EP_OK;
+}
+
+static size_t ll_slot_bytes(int max_tok, int H, int W, int E, int use_fp8, int K) {
+  const int e_local = E / W;
+  const size_t cap = (size_t)W * max_tok;
+  const size_t row = use_fp8 ? H : 2 * (size_t)H;
+  const size_t sc = use_fp8 ? (size_t)H / kGroup * 4 : 0;
+  size_t off = 0;
+  off = align_up(off + (size_t)e_local * cap * row, 4096);
+  off = align_up(off + (size_t)e_local * cap * sc, 4096);
+  off = align_up(off + (size_t)e_local * cap * 4, 4096);
+  off = align_up(off + (size_t)max_tok * K * 2 * H, 4096);
+  return off;
+}
+
+int make_ll_plan(const b200ep_ctx* c, int H, int K, int E, int max_tok, int use_fp8, LlPlan* p) {
+  const int W = c->world;
+  if (H <= 0 || H % kGroup != 0 || K <= 0 || K > kMaxTopk || E <= 0 || E % W != 0 || E / W > kMaxLocalExperts ||
+      max_tok <= 0) {
+    set_error("ll: unsupported shape H=%d K=%d E=%d world=%d max_tok=%d", H, K, E, W, max_tok);
+    return B200EP_ERR_ARG;
+  }
+  p->H = H;
+  p->K = K;
+  p->max_tok = max_tok;
+  p->use_fp8 = use_fp8;
+  p->e_local = E / W;
+  p->cap = W * max_tok;
+  p->row_bytes = use_fp8 ? H : 2 * H;
+  p->scale_bytes = use_fp8 ? H / kGroup * 4 : 0;
+  size_t off = 0;
+  p->off_x = off;
+  off = align_up(off + (size_t)p->e_local * p->cap * p->row_bytes, 4096);
+  p->off_scales = off;
+  off = align_up(off + (size_t)p->e_local * p->cap * p->scale_bytes, 4096);
+  p->off_src = off;
+  off = align_up(off + (size_t)p->e_local * p->cap * 4, 4096);
+  p->off_stage = off;
+  off = align_up(off + (size_t)max_tok * K * 2 * H, 4096);
+  if (off > c->slot_bytes) {
+    set_error("ll: symmetric region too small: slot needs %zu bytes, has %zu (size with b200ep_ll_size_hint)", off,
+              c->slot_bytes);
+    return B200EP_ERR_CAPACITY;
+  }
+  return B200EP_OK;
+}
+
+}  // namespace b200ep
+
+using namespace b200ep;
+
+extern "C" {
+
+const char* b200ep_last_error(void) { return g_err; }
+int b200ep_version(void) { return 100; }
+
+size_t b200ep_ll_size_hint(int max_tokens_per_rank, int H, int world, int E) {
+  if (world <= 0 || E <= 0 || E % world) return 0;
+  // bf16 rows and the largest top-k the library accepts: an upper bound for every mode
+  return kCtrlBytes + kNumSlots * (ll_slot_bytes(max_tokens_per_rank, H, world, E, 0, kMaxTopk) + 4096);
+}
+
+int b200ep_create(b200ep_ctx** out, int rank, int world, int device, size_t sym_bytes) {
+  if (!out || world < 1 || world > kMaxRanks || rank < 0 || rank >= world) {
+    set_error("create: bad rank/world %d/%d (world <= %d)", rank, world, kMaxRanks);
+    return B200EP_ERR_ARG;
+  }
+  if (sym_bytes < kCtrlBytes + (size_t)kNumSlots * (1 << 20)) {
+    set_error("create: sym_bytes %zu too small", sym_bytes);
+    return B200EP_ERR_ARG;
+  }
+  B200EP_CUDA(cudaSetDevice(device));
+  b200ep_ctx* c = new (std::nothrow) b200ep_ctx();
+  if (!c) {
+    set_error("create: out of host memory");
+    return B200EP_ERR_ARG;
+  }
+  memset(c, 0, sizeof(*c));
+  c->rank = rank;
+  c->world = world;
+  c->device = device;
+  B200EP_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device));
+  c->sm_limit = 0;
+  c->sym_bytes = sym_bytes / 4096 * 4096;
+  c->slot_bytes = (c->sym_bytes - kCtrlBytes) / kNumSlots / 4096 * 4096;
+  B200EP_CUDA(cudaMalloc(&c->sym, c->sym_bytes));
+  B200EP_CUDA(cudaMemset(c->sym, 0, kCtrlBytes));
+  B200EP_CUDA(cudaMalloc(&c->local, sizeof(LocalScratch)));
+  B200EP_CUDA(cudaMemset(c->local, 0, sizeof(LocalScratch)));
+  c->ll_local_bytes = 4 << 20;
+  B200EP_CUDA(cudaMalloc(&c->ll_local, c->ll_local_bytes));
+  B200EP_CUDA(cudaMemset(c->ll_local, 0, c->ll_local_bytes));
+  B200EP_CUDA(cudaHostAlloc(&c->host, sizeof(HostMirror), cudaHostAllocMapped));
+  memset((void*)c->host, 0, sizeof(HostMirror));
+  B200EP_CUDA(cudaHostGetDevicePointer((void**)&c->host_dev, (void*)c->host, 0));
+  B200EP_CUDA(cudaDeviceSynchronize());
+  c->peers.base[rank] = c->sym;
+  c->connected = (world == 1);
+  *out = c;
+  return B200EP_OK;
+}
+
+int b200ep_destroy(b200ep_ctx* c) {
+  if (!c) return B200EP_OK;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < c->world; ++r)
+    if (c->ipc_open[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
+  cudaFree(c->sym);
+  cudaFree(c->local);
+  cudaFree(c->ll_local);
+  cudaFreeHost((void*)c->host);
+  delete c;
+  return B200EP_OK;
+}
+
+int b200ep_export_handle(b200ep_ctx* c, void* out_handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == B200EP_IPC_HANDLE_BYTES, "handle size");
+  if (!c || !out_handle64) {
+    set_error("export_handle: null argument");
+    return B200EP_ERR_ARG;
+  }
+  B200EP_CUDA(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  B200EP_CUDA(cudaIpcGetMemHandle(&h, c->sym));
+  memcpy(out_handle64, &h, sizeof(h));
+  return B200EP_OK;
+}
+
+int b200ep_import_handles(b200ep_ctx* c, const void* handles, int n) {
+  if (!c || !handles || n != c->world) {
+    set_error("import_handles: need exactly world=%d handles", c ? c->world : -1);
+    return B200EP_ERR_ARG;
+  }
+  B200EP_CUDA(cudaSetDevice(c->device));
+  for (int r = 0; r < n; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles + (size_t)r * sizeof(h), sizeof(h));
+    void* p = nullptr;
+    B200EP_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peers.base[r] = (char*)p;
+    c->ipc_open[r] = true;
+  }
+  c->connected = true;
+  return B200EP_OK;
+}
+
+int b200ep_set_peer_ptrs(b200ep_ctx* c, void* const* dev_bases, int n) {
+  if (!c || !dev_bases || n != c->world) {
+    set_error("set_peer_ptrs: need exactly world=%d bases", c ? c->world : -1);
+    return B200EP_ERR_ARG;
+  }
+  for (int r = 0; r < n; ++r)
+    if (r != c->rank) c->peers.base[r] = (char*)dev_bases[r];
+  c->connected = true;
+  return B200EP_OK;
+}
+
+int b200ep_sym_base(b200ep_ctx* c, void** dev_base, size_t* bytes) {
+  if (!c) {
+    set_error("sym_base: null context");
+    return B200EP_ERR_ARG;
+  }
+  if (dev_base) *dev_base = c->sym;
+  if (bytes) *bytes = c->sym_bytes;
+  return B200EP_OK;
+}
+
+int b200ep_set_num_sms(b200ep_ctx* c, int num_sms) {
+  if (!c || num_sms < 0) {
+    set_error("set_num_sms: bad argument");
+    return B200EP_ERR_ARG;
+  }
+  c->sm_limit = num_sms;
+  return B200EP_OK;
+}
+
+int b200ep_ht_capacity(b200ep_ctx* c, int H, int K, int x_kind) {
+  HtPlan p;
+  if (!c || make_ht_plan(c, H, K, x_kind, &p) != B200EP_OK) return -1;
+  return p.t_cap;
+}
+
+int b200ep_ht_notify_wait(b200ep_ctx* c, int slot, int* num_recv_tokens, int32_t* per_expert, int32_t* rank_prefix,
+                          int timeout_ms) {
+  if (!c || slot < 0 || slot >= kNumSlots) {
+    set_error("ht_notify_wait: bad slot");
+    return B200EP_ERR_ARG;
+  }
+  const uint64_t want = c->epoch[kFlagHtNotify][slot];
+  auto t0 = std::chrono::steady_clock::now();
+  while (c->host->epoch[slot] < want) {
+    if (timeout_ms > 0 &&
+        std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count() >
+            timeout_ms) {
+      set_error("ht_notify_wait: rank %d timed out after %d ms waiting for the count exchange (epoch %llu)", c->rank,
+                timeout_ms, (unsigned long long)want);
+      return B200EP_ERR_TIMEOUT;
+    }
+    // also surface a dead stream instead of spinning on it
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) {
+      set_error("ht_notify_wait: CUDA error while waiting: %s", cudaGetErrorString(e));
+      return B200EP_ERR_CUDA;
+    }
+    std::this_thread::yield();
+  }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  if (num_recv_tokens) *num_recv_tokens = c->host->num_recv[slot];
+  if (rank_prefix) memcpy(rank_prefix, (const void*)c->host->rank_prefix[slot], sizeof(int32_t) * (c->world + 1));
+  if (per_expert) {
+    memcpy(per_expert, (const void*)c->host->recv_per_expert[slot], sizeof(int32_t) * c->ht_e_local[slot]);
+  }
+  return B200EP_OK;
+}
+
+}  // extern "C"

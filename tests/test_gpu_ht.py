@@ -1,0 +1,136 @@
+"""GPU parity: high-throughput dispatch + combine vs the CPU oracle, through the C ABI.
+W > 1 is emulated on one GPU (b200ep.LocalWorld: phases run rank by rank)."""
+import numpy as np
+import pytest
+import torch
+
+from _util import bf16_bits, bits_to_bf16, make_rank_inputs, u8
+from oracle import bits, combine, dispatch, fp8
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _inputs(W, Ts, H, E, K, seed, dist="uniform", idt=torch.int64, mask=0.0):
+    xs, ids, ws = [], [], []
+    for r in range(W):
+        x, i, w = make_rank_inputs(Ts[r], H, E, K, seed * 100 + r, dist=dist, world=W, id_dtype=idt, mask_frac=mask)
+        xs.append(x); ids.append(i); ws.append(w)
+    return xs, ids, ws
+
+
+def _check_dispatch(res, ref, kind, K):
+    for d, (rx, rs, ridx, rw, rsrc, per_expert, h) in enumerate(res):
+        o = ref[d]
+        assert h.num_recv == o["num_recv_tokens"]
+        assert list(h.rank_prefix) == list(o["rank_prefix"])
+        assert per_expert == list(o["num_recv_tokens_per_expert"])
+        if kind == "bf16":
+            assert np.array_equal(bf16_bits(rx), o["recv_x"])
+        else:
+            assert np.array_equal(u8(rx), o["recv_x"])
+            assert np.array_equal(rs.cpu().numpy().view(np.uint32), o["recv_x_scales"].view(np.uint32))
+        assert np.array_equal(ridx.cpu().numpy(), o["recv_topk_idx"])
+        assert np.array_equal(rw.cpu().numpy().view(np.uint32), o["recv_topk_weights"].view(np.uint32))
+        assert np.array_equal(rsrc.cpu().numpy(), o["recv_src_idx"])
+
+
+@pytest.mark.parametrize("W", [1, 2, 4, 8])
+@pytest.mark.parametrize("kind", ["quant", "fp8", "bf16"])
+def test_ht_dispatch_combine_bit_exact(W, kind):
+    from b200ep import LocalWorld
+
+    H, E, K = 1024, 32, 8   # BASELINE config #1 shape (granite): 32 experts, top-8, hidden 1024
+    world = LocalWorld(W, sym_bytes=192 << 20)
+    try:
+        for it, (dist, mask, idt) in enumerate([("uniform", 0.0, torch.int64), ("one_rank", 0.0, torch.int32),
+                                               ("zipf", 0.2, torch.int64)]):
+            Ts = [max(0, 301 - 37 * r) if r != 1 else 0 for r in range(W)]  # ragged, one empty rank
+            if W == 1:
+                Ts = [257]
+            xs, ids, ws = _inputs(W, Ts, H, E, K, seed=it + 10 * W, dist=dist, idt=idt, mask=mask)
+            xb = [bf16_bits(x) for x in xs]
+            if kind == "bf16":
+                ref = dispatch.ht_dispatch(xb, [i.numpy() for i in ids], [w.numpy() for w in ws], E)
+                res = world.dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], [w.to(DEV) for w in ws], E)
+            else:
+                qs = [fp8.group_quant_fp8(b, formula="div") for b in xb]
+                ref = dispatch.ht_dispatch([q for q, _ in qs], [i.numpy() for i in ids], [w.numpy() for w in ws], E,
+                                           scales=[s for _, s in qs])
+                if kind == "quant":
+                    res = world.dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], [w.to(DEV) for w in ws], E,
+                                         quantize=True)
+                else:
+                    xq = [torch.from_numpy(q).view(torch.float8_e4m3fn).to(DEV) for q, _ in qs]
+                    sq = [torch.from_numpy(s).to(DEV) for _, s in qs]
+                    res = world.dispatch(xq, [i.to(DEV) for i in ids], [w.to(DEV) for w in ws], E, x_scales=sq)
+            _check_dispatch(res, ref, kind, K)
+            # expert stand-in: y = bf16(row-dependent function of what was received)
+            ys_np = []
+            for d in range(W):
+                o = ref[d]
+                if kind == "bf16":
+                    v = bits.bf16_to_f32(o["recv_x"])
+                else:
+                    v = fp8.dequant_fp8(o["recv_x"], o["recv_x_scales"])
+                v = v * (1.0 + 0.25 * d) + 0.125 * o["recv_topk_weights"].sum(1, keepdims=True)
+                ys_np.append(bits.f32_to_bf16(v.astype(np.float32)))
+            outs = world.combine([bits_to_bf16(y, DEV) for y in ys_np], [r[-1] for r in res])
+            ref_out = combine.ht_combine(ys_np, ref, Ts)
+            for r in range(W):
+                assert np.array_equal(bf16_bits(outs[r]), ref_out[r]), f"combine differs on rank {r}"
+    finally:
+        world.destroy()
+
+
+@pytest.mark.parametrize("W", [1, 2])
+def test_ht_full_size_properties(W):
+    """BASELINE config #2 shape (DeepSeek-V3 layer: hidden 7168, 256 experts, top-8, 4096 tokens/rank).
+    Size-independent checks: counts add up, source indices ascending per source rank, every received
+    row dequantises to its source row, combine(identity experts) == (#destination ranks) * dequant(x)."""
+    from b200ep import LocalWorld
+
+    T, H, E, K = 4096, 7168, 256, 8
+    world = LocalWorld(W, sym_bytes=(1 << 30) if W == 1 else (1 << 30))
+    try:
+        xs, ids, ws = _inputs(W, [T] * W, H, E, K, seed=77)
+        res = world.dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], [w.to(DEV) for w in ws], E, quantize=True)
+        owner = [(i // (E // W)) for i in ids]
+        ndst = [torch.stack([(o == d).any(1) for d in range(W)], 1).sum(1) for o in owner]
+        total = 0
+        ys = []
+        for d, (rx, rs, ridx, rw, rsrc, per_expert, h) in enumerate(res):
+            M = h.num_recv
+            total += M
+            assert sum(per_expert) == int((ridx >= 0).sum())
+            deq = (rx.float().view(M, H // 128, 128) * rs[:, :, None]).view(M, H)
+            for s in range(W):
+                a, b = h.rank_prefix[s], h.rank_prefix[s + 1]
+                t = rsrc[a:b].long()
+                assert bool((t[1:] > t[:-1]).all())
+                src = xs[s].to(DEV)[t].float()
+                # e4m3 with a per-128 scale: relative step 2^-3 of the group amax at worst
+                amax = src.view(b - a, H // 128, 128).abs().amax(2, keepdim=True).expand(-1, -1, 128).reshape(b - a, H)
+                assert bool(((deq[a:b] - src).abs() <= amax * 0.0625 + 1e-6).all())
+            assert bool(((rw > 0) == (ridx >= 0)).all())
+            ys.append(deq.to(torch.bfloat16))
+        assert total == int(sum(int(n.sum()) for n in ndst))
+        outs = world.combine(ys, [r[-1] for r in res])
+        for r in range(W):
+            ref = xs[r].to(DEV).float() * ndst[r].to(DEV)[:, None]
+            err = (outs[r].float() - ref).abs().max().item()
+            assert err <= 0.08 * ref.abs().max().item(), err
+    finally:
+        world.destroy()
+
+
+def test_ht_capacity_error_is_loud():
+    from b200ep import B200EPError, LocalWorld
+
+    world = LocalWorld(1, sym_bytes=16 << 20)
+    try:
+        x, ids, w = make_rank_inputs(4096, 7168, 256, 8, 1)
+        with pytest.raises(B200EPError, match="capacity"):
+            world.bufs[0].dispatch(x.to(DEV), ids.to(DEV), w.to(DEV), 256, quantize=True)
+    finally:
+        world.destroy()
