@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""Benchmark of the wide-EP MoE dispatch+combine hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One step = one high-throughput dispatch + combine of the synthetic DeepSeek-V3 MoE layer of
+BASELINE.json configs[1] (hidden 7168, 256 experts, top-8, 4096 tokens/rank, bf16 -> FP8-128):
+routing layout kernel, count exchange, fused quantise+dispatch, combine.  EP size = N (one
+process per GPU, launched by torchrun for N > 1; CUDA-IPC peers, NCCL only for bootstrap/barriers).
+
+Printed JSON (one line, rank 0):
+  value      whole-job tokens/s, inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e        same metric through the public API with HOST buffers: pinned->device copies of the
+             step's inputs and a device->host read of the combined output inside the timed region
+             (the expert stand-in between dispatch and combine -- a dequantise -- is also inside)
+  roofline   dominant kernel vs measured HBM peak (N=1) or NVLink per-direction peak (N>1)
+  cpu_baseline  the reference's CPU dispatch/combine (oracle/cpu_reference.py, a port of vLLM
+             cpu_fused_moe_torch) timed on this box's host cores on a bounded sample (N=1 only)
+  ll         low-latency decode mode, 128 tokens/rank, CUDA-graph replay p50/p99 (informative)
+--impl reference times that CPU port alone, all host threads, and prints the same line shape.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "llm-d_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+T, H, E, K = 4096, 7168, 256, 8
+LL_T = 128
+NVLINK_PEAK_GBS = 770.0  # measured peer-copy GB/s per direction on this pool (B200_PROFILING.md); nominal 900
+METRIC = "dispatch+combine tokens/s"
+WORKLOAD = "synthetic DeepSeek-V3 MoE layer (hidden 7168, 256 experts, top-8), 4096 tokens/rank bf16->FP8 high-throughput dispatch+combine"
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "MEASURED_PEAKS.json"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+def make_inputs(seed: int, tokens: int = T):
+    g = torch.Generator().manual_seed(seed)
+    x = (torch.randn(tokens, H, generator=g) * (torch.rand(tokens, 1, generator=g) * 4)).to(torch.bfloat16)
+    logits = torch.randn(tokens, E, generator=g)
+    vals, ids = torch.topk(logits, K, dim=-1, sorted=False)
+    w = torch.softmax(vals, dim=-1).float()
+    return x.contiguous(), ids.to(torch.int64).contiguous(), w.contiguous()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (profiling recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [q.strip() for q in ln.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0])); mx = float(p[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(sample_tokens: int, repeats: int, threads: int | None = None):
+    """The reference's CPU dispatch/combine on a bounded sample of the same workload."""
+    from oracle.cpu_reference import cpu_dispatch_combine
+
+    n = threads or os.cpu_count() or 1
+    torch.set_num_threads(n)
+    x, ids, w = make_inputs(1234, sample_tokens)
+    ids32 = ids.to(torch.int32)
+    cpu_dispatch_combine(x, w, ids32, E)  # warm-up
+    best, times = None, []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        cpu_dispatch_combine(x, w, ids32, E)
+        dt = time.perf_counter() - t0
+        times.append(dt)
+        best = dt if best is None else min(best, dt)
+    return {
+        "value": sample_tokens / best,
+        "unit": "tokens/s",
+        "cores": torch.get_num_threads(),
+        "kind": "port",
+        "sample": f"{sample_tokens} tokens x hidden {H}, top-{K} of {E} experts, bf16, identity experts, "
+                  f"best of {repeats} (mean {sum(times) / len(times):.3f} s/step); "
+                  "port of vLLM cpu_fused_moe_torch (cpu_fused_moe.py:444-449,467-481)",
+    }, best
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    from oracle.cpu_reference import cpu_dispatch_combine
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    sample = 4096
+    x, ids, w = make_inputs(1234, sample)
+    ids32 = ids.to(torch.int32)
+    for _ in range(warm):
+        cpu_dispatch_combine(x, w, ids32, E)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_dispatch_combine(x, w, ids32, E)
+    dt = (time.perf_counter() - t0) / steps
+    val = sample / dt
+    base = {"value": val, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{sample} tokens/step x {steps} steps, hidden {H}, top-{K} of {E}, bf16, identity experts"}
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16 (fp32 reduce)", "data": "synthetic", "config": {"workload": WORKLOAD, "ep_size": 1, "host": "cpu"},
+        "cpu_baseline": base, "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200ep")
+    ap.add_argument("--no-ll", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sym-gb", type=float, default=0.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch.distributed as dist
+
+    import b200ep
+    from b200ep import _lib as L
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torchrun for N>1)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.new_group(backend="gloo")  # host channel for the 64-byte IPC handles
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    steps, warm = max(1, args.steps), max(3, args.warmup)
+    W = world
+    # per-slot need: W*T receive rows + T*W stage rows; size the region for it with headroom
+    need = 2 * (W * T * (H + H // 32 + K * 12 + 4) + T * W * 2 * H) + (64 << 20)
+    ll_need = b200ep.Buffer.ll_size_hint(LL_T, H, W, E)
+    sym = int(args.sym_gb * 2**30) if args.sym_gb else int(max(need, ll_need) * 1.1)
+    buf = b200ep.Buffer(group, sym_bytes=sym, device=local, rank=rank, world=world)
+
+    NBUF = 4  # rotate inputs so a step never finds its inputs in the 126 MB L2
+    xs, idss, wss = [], [], []
+    for b in range(NBUF):
+        x, ids, w = make_inputs(1000 * b + rank)
+        xs.append(x.to(dev)); idss.append(ids.to(dev)); wss.append(w.to(dev))
+    y_pool = torch.randn(W * T if W > 1 else T, H, device=dev).to(torch.bfloat16)  # expert outputs (resident)
+    out = torch.empty(T, H, dtype=torch.bfloat16, device=dev)
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    k_disp, k_comb, remote_copies = [], [], []
+
+    def step(i, timed):
+        b = i % NBUF
+        lay = buf.get_dispatch_layout(idss[b], E)
+        h, a = buf._dispatch_prepare(xs[b], idss[b], wss[b], E, None, True, False, lay)
+        buf.ht_notify(h.slot, lay)
+        buf._dispatch_after_notify(h)
+        e0, e1, e2, e3 = ev(), ev(), ev(), ev()
+        e0.record()
+        buf.ht_dispatch_launch(h, *a, L.PHASE_ALL)
+        e1.record()
+        y = y_pool[: h.num_recv]
+        e2.record()
+        buf.combine(y, h, out)
+        e3.record()
+        if timed:
+            k_disp.append((e0, e1)); k_comb.append((e2, e3))
+            remote_copies.append(h.num_recv - (h.rank_prefix[rank + 1] - h.rank_prefix[rank]))
+
+    for i in range(warm):
+        step(i, False)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    t_start, t_end = ev(), ev()
+    t_start.record()
+    for i in range(steps):
+        step(warm + i, True)
+    t_end.record()
+    torch.cuda.synchronize()
+    ms = t_start.elapsed_time(t_end)
+    clocks = sampler.stop() if rank == 0 else None
+    tms = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    barrier()
+    ms_total = float(tms.item())
+    ms_step = ms_total / steps
+    value = world * T * steps / (ms_total / 1e3)
+
+    d_ms = sorted(a.elapsed_time(b) for a, b in k_disp)
+    c_ms = sorted(a.elapsed_time(b) for a, b in k_comb)
+    d_avg, c_avg = sum(d_ms) / len(d_ms), sum(c_ms) / len(c_ms)
+    peaks, peak_src = measured_peaks()
+    if world == 1:
+        # algorithmic bytes per launch: dispatch T*(2H + H + 4H/128); combine T*(2H + 2H)
+        db, cb = T * (2 * H + H + 4 * H // 128), T * (2 * H + 2 * H)
+        peak, bound, unit_note = float(peaks["hbm_gbs"]), "hbm", f"HBM copy peak from {peak_src}"
+    else:
+        r = sum(remote_copies) / len(remote_copies)  # remote copies actually made per step by this rank's peers -> me
+        db, cb = r * (H + 4 * H // 128), r * 2 * H
+        peak, bound, unit_note = NVLINK_PEAK_GBS, "nvlink", "measured peer-copy GB/s per direction (guide); 900 nominal"
+    d_gbs, c_gbs = db / (d_avg * 1e-3) / 1e9, cb / (c_avg * 1e-3) / 1e9
+    dominant = "ht_combine (send+recv kernels)" if c_avg >= d_avg else "ht_dispatch_send_kernel"
+    dom_gbs = c_gbs if c_avg >= d_avg else d_gbs
+    roofline = {
+        "bound": bound, "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak, "traffic": None,
+        "kernel": dominant, "peak_source": unit_note,
+        "kernels": {
+            "dispatch": {"ms": d_avg, "algorithmic_bytes": db, "gbs": d_gbs, "frac": d_gbs / peak},
+            "combine": {"ms": c_avg, "algorithmic_bytes": cb, "gbs": c_gbs, "frac": c_gbs / peak},
+        },
+        "step_frac": (db + cb) / (ms_step * 1e-3) / 1e9 / peak,
+    }
+
+    # ---- end to end through the public API with host buffers
+    hx = [x.cpu().pin_memory() for x in xs[:2]]
+    hi = [i.cpu().pin_memory() for i in idss[:2]]
+    hw = [w.cpu().pin_memory() for w in wss[:2]]
+    hout = torch.empty(T, H, dtype=torch.bfloat16).pin_memory()
+    dx, di, dw = torch.empty_like(xs[0]), torch.empty_like(idss[0]), torch.empty_like(wss[0])
+
+    def e2e_step(i):
+        b = i % 2
+        dx.copy_(hx[b], non_blocking=True); di.copy_(hi[b], non_blocking=True); dw.copy_(hw[b], non_blocking=True)
+        rx, rs, ridx, rw, per_expert, h = buf.dispatch(dx, di, dw, E, quantize=True)
+        M = h.num_recv
+        y = (rx.float().view(M, H // 128, 128) * rs[:, :, None]).view(M, H).to(torch.bfloat16)  # expert stand-in
+        buf.combine(y, h, out)
+        hout.copy_(out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    e2e_steps = max(3, min(steps, 10))
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    s0, s1 = ev(), ev()
+    s0.record()
+    for i in range(e2e_steps):
+        e2e_step(i)
+    s1.record()
+    torch.cuda.synchronize()
+    e_ms = torch.tensor([s0.elapsed_time(s1)], device=dev)
+    if world > 1:
+        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+    e2e = {
+        "value": world * T * e2e_steps / (float(e_ms.item()) / 1e3), "unit": "tokens/s",
+        "h2d_bytes_per_step": dx.numel() * 2 + di.numel() * 8 + dw.numel() * 4, "d2h_bytes_per_step": out.numel() * 2,
+        "ms_per_step": float(e_ms.item()) / e2e_steps, "wall_s": e2e_wall,
+    }
+
+    # ---- low-latency decode mode: CUDA-graph replay
+    ll = None
+    if not args.no_ll:
+        try:
+            ll = bench_ll(buf, rank, world, dev, barrier)
+        except Exception as ex:  # keep the headline number even if the informative part fails
+            ll = {"error": repr(ex)[:300]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu, _ = cpu_baseline(1024, 5)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": steps, "warmup": warm,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16 in, fp8 e4m3 + fp32 scales dispatched, bf16 combined with fp32 accumulate",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "ep_size": world, "tokens_per_rank": T, "hidden": H, "experts": E, "topk": K,
+                       "l2": f"{NBUF} rotating input sets ({NBUF * (T * H * 2) >> 20} MiB of x) > 126 MB L2",
+                       "tokens_per_s_per_gpu": value / world},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
+            "gpu_launches": steps * 7, "ll": ll,
+        }
+        print(json.dumps(line))
+    buf.destroy()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_ll(buf, rank, world, dev, barrier, replays: int = 200):
+    """128 tokens/rank low-latency dispatch+combine captured in ONE CUDA graph, replayed; per-replay
+    time from CUDA events (max over ranks of the p50 is reported)."""
+    import torch.distributed as dist
+
+    x, ids, w = make_inputs(99 + rank, LL_T)
+    x, ids, w = x.to(dev), ids.to(dev), w.to(dev)
+    el, cap = E // world, world * LL_T
+    y = torch.randn(el, cap, H, device=dev).to(torch.bfloat16)
+    out = torch.empty(LL_T, H, dtype=torch.bfloat16, device=dev)
+    from b200ep import LlHandle
+    from b200ep import _lib as L
+
+    h = LlHandle(0, LL_T, H, K, E, LL_T, True)
+
+    def one():
+        buf.ll_dispatch_launch(h, x, ids, False, L.LL_PHASE_ALL)
+        buf.low_latency_combine(y, ids, w, h, out, phases=L.PHASE_ALL)
+
+    s = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(s):
+        for _ in range(3):
+            one()
+        s.synchronize()
+        barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s, capture_error_mode="relaxed"):
+            one()
+        barrier()
+        for _ in range(10):
+            g.replay()
+        s.synchronize()
+        barrier()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(replays + 1)]
+        evs[0].record(s)
+        for i in range(replays):
+            g.replay()
+            evs[i + 1].record(s)
+        s.synchronize()
+    us = sorted(evs[i].elapsed_time(evs[i + 1]) * 1e3 for i in range(replays))
+    p50, p99 = us[len(us) // 2], us[int(len(us) * 0.99) - 1]
+    t = torch.tensor([p50, p99], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    barrier()
+    # algorithmic floor: per (token, expert) message H + 4H/128 out, 2H back, (W-1)/W remote
+    return {"tokens_per_rank": LL_T, "mode": "fp8 dispatch + bf16 combine, one CUDA graph (5 kernels), replayed",
+            "p50_us": float(t[0].item()), "p99_us": float(t[1].item()), "replays": replays, "ep_size": world}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

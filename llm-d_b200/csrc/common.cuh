@@ -134,11 +134,14 @@ __device__ __forceinline__ void wait_flag_sys(const uint64_t* flag, uint64_t wan
   }
 }
 
-// "All CTAs of this kernel have finished their stores" -> signal every peer.
+// Call epochs live in PRIVATE device memory (LocalScratch::epoch) and are advanced by the kernels
+// themselves, never passed as launch arguments: a captured CUDA graph replays correctly.
+//
+// "All CTAs of this kernel have finished their stores" -> signal every peer with the next epoch.
 // Call with all threads of the CTA after the CTA's last store (and after bulk_wait_all()).
-// counter: private device word, must be 0 before the kernel and is reset to 0 by the last CTA.
-__device__ __forceinline__ void cta_done_then_signal(unsigned* counter, const Peers& peers, int world, int cat, int slot,
-                                                     int me, uint64_t epoch) {
+// counter: private device word, 0 before the kernel, reset to 0 by the last CTA.
+__device__ __forceinline__ void cta_done_then_signal(unsigned* counter, unsigned long long* epoch_ptr,
+                                                     const Peers& peers, int world, int cat, int slot, int me) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
@@ -146,18 +149,23 @@ __device__ __forceinline__ void cta_done_then_signal(unsigned* counter, const Pe
     if (prev == gridDim.x - 1) {
       __threadfence_system();
       *counter = 0;
+      const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
       for (int d = 0; d < world; ++d)
         st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[d] + flag_off(cat, slot, me)), epoch);
+      *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
     }
   }
 }
 
-// All CTAs wait for every source rank's flag (flags live in MY region).
+// All CTAs wait for every source rank's flag (flags live in MY region).  The epoch to wait for is
+// the one this rank's own send of the same call already stored (stream order guarantees that).
 __device__ __forceinline__ void cta_wait_all_sources(const char* my_base, int world, int cat, int slot, int me,
-                                                     uint64_t epoch) {
-  if ((int)threadIdx.x < world)
+                                                     const unsigned long long* epoch_ptr) {
+  if ((int)threadIdx.x < world) {
+    const uint64_t epoch = *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr);
     wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(cat, slot, threadIdx.x)), epoch, cat, me,
                   threadIdx.x);
+  }
   __syncthreads();
 }
 
@@ -178,8 +186,8 @@ __device__ __forceinline__ float absmax8(const float (&f)[8]) {
 }
 __device__ __forceinline__ float group_scale(float amax, bool ue8m0) {
   float s = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
-  if (ue8m0) {  // 2^ceil(log2 s), exact on the bit pattern
-    uint32_t u = __float_as_uint(s);
+  if (ue8m0) {  // 2^ceil(log2 max(s, 1e-10)), exact on the bit pattern (vLLM clamps the scale again here)
+    uint32_t u = __float_as_uint(fmaxf(s, 1e-10f));
     u = (u & 0x7f800000u) + ((u & 0x007fffffu) ? 0x00800000u : 0u);
     s = __uint_as_float(u);
   }
@@ -221,6 +229,7 @@ struct LocalScratch {
   unsigned long long layout_ticket;                          // monotonically increasing block ticket
   unsigned long long layout_pub[kMaxLayoutBlocks][kMaxRanks]; // (epoch << 32 | count) per block and rank
   HtMeta ht[kNumSlots];
+  unsigned long long epoch[kNumFlagCat][kNumSlots];          // call epochs, advanced on the device
 };
 // pinned host mirror of the count exchange result
 struct HostMirror {

@@ -31,7 +31,9 @@ namespace b200ep {
 // ------------------------------------------------------------------ notify
 __global__ void __launch_bounds__(256)
     ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, const int32_t* __restrict__ tok_per_rank,
-                          const int32_t* __restrict__ tok_per_expert, uint64_t epoch) {
+                          const int32_t* __restrict__ tok_per_expert, unsigned long long* epoch_ptr) {
+  __shared__ unsigned long long s_epoch;
+  if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
   for (int d = 0; d < W; ++d) {
     char* ctrl = peers.base[d];
     int32_t* cr = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntRankOff) + ((size_t)slot * kMaxRanks + me) * kMaxRanks;
@@ -42,14 +44,15 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   if ((int)threadIdx.x < W) {
     __threadfence_system();
-    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[threadIdx.x] + flag_off(kFlagHtNotify, slot, me)), epoch);
+    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[threadIdx.x] + flag_off(kFlagHtNotify, slot, me)), s_epoch);
   }
+  if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = s_epoch;
 }
 
 __global__ void __launch_bounds__(256)
     ht_notify_recv_kernel(const char* my_base, int W, int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
-                          uint64_t epoch) {
-  cta_wait_all_sources(my_base, W, kFlagHtNotify, slot, me, epoch);
+                          const unsigned long long* epoch_ptr) {
+  cta_wait_all_sources(my_base, W, kFlagHtNotify, slot, me, epoch_ptr);
   const int32_t* cr = reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntRankOff) + (size_t)slot * kMaxRanks * kMaxRanks;
   const int32_t* ce =
       reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntExpOff) + (size_t)slot * kMaxRanks * kMaxLocalExperts;
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   if (tid == 0) {
     __threadfence_system();
-    host->epoch[slot] = epoch;
+    host->epoch[slot] = *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr);
   }
 }
 
@@ -98,7 +101,7 @@ struct HtDispatchArgs {
   const HtMeta* meta;
   unsigned* done;
   size_t slot_off;  // kCtrlBytes + slot * slot_bytes
-  uint64_t epoch;
+  unsigned long long* epoch_ptr;
   int T, W, me, slot, e_local, ue8m0, ids_i64;
 };
 
@@ -226,11 +229,12 @@ __global__ void __launch_bounds__(512) ht_dispatch_send_kernel(const __grid_cons
     }
   }
   bulk_wait_all();
-  cta_done_then_signal(a.done, a.peers, W, kFlagHtData, a.slot, a.me, a.epoch);
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
 }
 
-__global__ void wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me, uint64_t epoch) {
-  cta_wait_all_sources(my_base, W, cat, slot, me, epoch);
+__global__ void wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
+                                    const unsigned long long* epoch_ptr) {
+  cta_wait_all_sources(my_base, W, cat, slot, me, epoch_ptr);
 }
 
 // ------------------------------------------------------------------ combine
@@ -244,7 +248,7 @@ struct HtCombineArgs {
   const HtMeta* meta;
   unsigned* done;
   size_t slot_off;
-  uint64_t epoch;
+  unsigned long long* epoch_ptr;
   int T, W, me, slot;
 };
 
@@ -291,7 +295,7 @@ __global__ void __launch_bounds__(512) ht_combine_send_kernel(const __grid_const
     }
   }
   bulk_wait_all();
-  cta_done_then_signal(a.done, a.peers, W, kFlagHtComb, a.slot, a.me, a.epoch);
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtComb, a.slot, a.me);
 }
 
 __device__ __forceinline__ void acc8(float (&acc)[8], const int4& v) {
@@ -312,7 +316,7 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 
 // Source rank: out[t] = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ).
 __global__ void __launch_bounds__(512) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
-  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch);
+  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H;
@@ -387,15 +391,15 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
       set_error("ht_notify: null counts");
       return B200EP_ERR_ARG;
     }
-    const uint64_t ep = ++c->epoch[kFlagHtNotify][slot];
+    ++c->epoch[kFlagHtNotify][slot];  // host mirror of the device epoch, for b200ep_ht_notify_wait
     c->ht_e_local[slot] = el;
     ht_notify_send_kernel<<<1, 256, 0, st>>>(c->peers, c->world, c->rank, slot, el, dev_tokens_per_rank,
-                                             dev_tokens_per_expert, ep);
+                                             dev_tokens_per_expert, &c->local->epoch[kFlagHtNotify][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_PHASE_RECV) {
     ht_notify_recv_kernel<<<1, 256, 0, st>>>(c->sym, c->world, c->rank, slot, el, &c->local->ht[slot], c->host_dev,
-                                             c->epoch[kFlagHtNotify][slot]);
+                                             &c->local->epoch[kFlagHtNotify][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
@@ -445,7 +449,7 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.meta = &c->local->ht[slot];
     a.done = &c->local->done[0 + slot];
     a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
-    a.epoch = ++c->epoch[kFlagHtData][slot];
+    a.epoch_ptr = &c->local->epoch[kFlagHtData][slot];
     a.T = T;
     a.W = c->world;
     a.me = c->rank;
@@ -471,7 +475,7 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     if (rc) return rc;
   }
   if (phases & B200EP_PHASE_RECV) {
-    wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, c->epoch[kFlagHtData][slot]);
+    wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, &c->local->epoch[kFlagHtData][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
@@ -525,9 +529,9 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.W = c->world;
   a.me = c->rank;
   a.slot = slot;
+  a.epoch_ptr = &c->local->epoch[kFlagHtComb][slot];
   const int row_bytes = 2 * H;
   if (phases & B200EP_PHASE_SEND) {
-    a.epoch = ++c->epoch[kFlagHtComb][slot];
     int warps = 200 * 1024 / row_bytes;
     if (warps > 16) warps = 16;
     if (warps < 1) warps = 1;
@@ -544,7 +548,6 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
       set_error("ht_combine: null pointer");
       return B200EP_ERR_ARG;
     }
-    a.epoch = c->epoch[kFlagHtComb][slot];
     const int warps = 16;
     const int grid = grid_for(c, T, warps, 2);
     ht_combine_recv_kernel<<<grid, warps * 32, 0, st>>>(a);

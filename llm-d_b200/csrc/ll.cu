@@ -42,7 +42,7 @@ static_assert(sizeof(LlScratch) * kNumSlots <= (4u << 20), "ll scratch");
 template <typename IdT>
 __global__ void __launch_bounds__(1024)
     ll_count_kernel(Peers peers, int W, int me, int slot, const IdT* __restrict__ ids, int T, int K, int E,
-                    LlScratch* sc, uint64_t epoch) {
+                    LlScratch* sc, unsigned long long* epoch_ptr) {
   extern __shared__ int s_ids[];  // transposed [K][Tp] so that lanes read consecutive words
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   const int Tp = (T + 31) / 32 * 32;
@@ -71,10 +71,13 @@ __global__ void __launch_bounds__(1024)
     for (int i = tid; i < E; i += blockDim.x) ce[i] = sc->cnt_mine[i];
   }
   __syncthreads();
+  const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
   if (tid < W) {
     __threadfence_system();
     st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[tid] + flag_off(kFlagLlCount, slot, me)), epoch);
   }
+  __syncthreads();
+  if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
 }
 
 struct LlDispatchArgs {
@@ -85,7 +88,7 @@ struct LlDispatchArgs {
   LlScratch* sc;
   unsigned* done;
   size_t slot_off;
-  uint64_t epoch_cnt, epoch_data;
+  unsigned long long *epoch_cnt_ptr, *epoch_data_ptr;
   int T, W, me, slot, E, ue8m0, ids_i64;
 };
 
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
       fence_proxy_async_smem();
     }
     if (!counts_ready) {
-      cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt);
+      cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt_ptr);
       counts_ready = true;
       if (blockIdx.x == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
         for (int el = tid; el < e_local; el += blockDim.x) {
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
     }
   }
   if (tid < K) bulk_wait_all();
-  cta_done_then_signal(a.done, a.peers, W, kFlagLlData, a.slot, a.me, a.epoch_data);
+  cta_done_then_signal(a.done, a.epoch_data_ptr, a.peers, W, kFlagLlData, a.slot, a.me);
 }
 
 struct LlCombineArgs {
@@ -189,7 +192,7 @@ struct LlCombineArgs {
   const LlScratch* sc;
   unsigned* done;
   size_t slot_off;
-  uint64_t epoch;
+  unsigned long long* epoch_ptr;
   int T, W, me, slot, E, ids_i64;
 };
 
@@ -234,13 +237,13 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
     (void)K;
   }
   bulk_wait_all();
-  cta_done_then_signal(a.done, a.peers, W, kFlagLlComb, a.slot, a.me, a.epoch);
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagLlComb, a.slot, a.me);
 }
 
 // out[t] = bf16( sum_k w[t,k] * row(t,k) ): fp32 multiply, fp32 add, k ascending.
 // A warp owns (token, 512-byte column block) so that 128 tokens still fill the GPU.
 __global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_constant__ LlCombineArgs a) {
-  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch);
+  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
@@ -299,8 +302,9 @@ __global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_const
   }
 }
 
-__global__ void ll_wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me, uint64_t epoch) {
-  cta_wait_all_sources(my_base, W, cat, slot, me, epoch);
+__global__ void ll_wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
+                                       const unsigned long long* epoch_ptr) {
+  cta_wait_all_sources(my_base, W, cat, slot, me, epoch_ptr);
 }
 
 }  // namespace b200ep
@@ -347,7 +351,7 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
   LlScratch* sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
   if (phases & B200EP_LL_PHASE_COUNT) {
     c->ll_plan[slot] = plan;
-    const uint64_t ep = ++c->epoch[kFlagLlCount][slot];
+    unsigned long long* ep = &c->local->epoch[kFlagLlCount][slot];
     const int Tp = (T + 31) / 32 * 32;
     const size_t smem = (size_t)K * Tp * 4;
     if (ids_i64) {
@@ -370,8 +374,8 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
     a.sc = sc;
     a.done = &c->local->done[4 + slot];
     a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
-    a.epoch_cnt = c->epoch[kFlagLlCount][slot];
-    a.epoch_data = ++c->epoch[kFlagLlData][slot];
+    a.epoch_cnt_ptr = &c->local->epoch[kFlagLlCount][slot];
+    a.epoch_data_ptr = &c->local->epoch[kFlagLlData][slot];
     a.T = T;
     a.W = c->world;
     a.me = c->rank;
@@ -391,7 +395,7 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_LL_PHASE_RECV) {
-    ll_wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagLlData, slot, c->rank, c->epoch[kFlagLlData][slot]);
+    ll_wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagLlData, slot, c->rank, &c->local->epoch[kFlagLlData][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
@@ -445,13 +449,13 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
   a.slot = slot;
   a.E = E;
   a.ids_i64 = ids_i64;
+  a.epoch_ptr = &c->local->epoch[kFlagLlComb][slot];
   const int row_bytes = 2 * H;
   if (phases & B200EP_PHASE_SEND) {
     if (!dev_y) {
       set_error("ll_combine: null dev_y");
       return B200EP_ERR_ARG;
     }
-    a.epoch = ++c->epoch[kFlagLlComb][slot];
     int warps = 200 * 1024 / row_bytes;
     if (warps > 16) warps = 16;
     if (warps < 1) warps = 1;
@@ -466,7 +470,6 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
       set_error("ll_combine: null pointer");
       return B200EP_ERR_ARG;
     }
-    a.epoch = c->epoch[kFlagLlComb][slot];
     const int nblk = (row_bytes / 16 + 31) / 32;
     int grid = (T * nblk + 7) / 8;
     grid = ll_grid(c, grid) * (grid > c->num_sms ? 2 : 1);

@@ -32,8 +32,10 @@ GROUP = 128
 
 
 def ceil_pow2_f32(s: np.ndarray) -> np.ndarray:
-    """Smallest power of two >= s for positive normal float32 s, bit-exact."""
-    s = np.ascontiguousarray(s, dtype=np.float32)
+    """Smallest power of two >= max(s, 1e-10) for positive normal float32 s, bit-exact.
+    (vLLM's CUDA op computes exp2f(ceilf(log2f(fmaxf(fabsf(s), 1e-10f)))): the scale is clamped a
+    second time in the UE8M0 branch.)"""
+    s = np.maximum(np.ascontiguousarray(s, dtype=np.float32), EPS)
     u = s.view(np.uint32)
     mant = u & np.uint32(0x007FFFFF)
     exp = u & np.uint32(0x7F800000)

@@ -100,5 +100,8 @@ def test_quant_matches_vllm_cuda_op(dev):
     for ue in (False, True):
         rq, rs = per_token_group_quant_fp8(x, 128, use_ue8m0=ue)
         q, s = Buffer.quant_fp8(x, ue8m0=ue)
-        assert torch.equal(rs.contiguous().view(torch.int32), s.view(torch.int32)), f"scales differ (ue8m0={ue})"
+        bad = (rs.contiguous().view(torch.int32) != s.view(torch.int32)).nonzero()
+        assert bad.numel() == 0, (f"scales differ (ue8m0={ue}) at {bad[:5].tolist()}: "
+                                  f"vllm {[rs[i, j].item() for i, j in bad[:5].tolist()]} "
+                                  f"ours {[s[i, j].item() for i, j in bad[:5].tolist()]}")
         assert torch.equal(rq.view(torch.uint8), q.view(torch.uint8)), f"fp8 bytes differ (ue8m0={ue})"
