@@ -78,6 +78,20 @@ class LlHandle:
     keep: Any = None
 
 
+def exchange_handles(group, mine: bytes) -> bytes:
+    """All-gather one 64-byte CUDA-IPC handle per rank over a host process group (gloo or nccl);
+    returns the world*64-byte blob in rank order.  Same pattern as vLLM's custom all-reduce
+    bootstrap (vllm/distributed/device_communicators/custom_all_reduce.py:296-315)."""
+    import torch.distributed as dist
+
+    assert len(mine) == 64
+    world = dist.get_world_size(group)
+    gathered: list = [None] * world
+    dist.all_gather_object(gathered, mine, group=group)
+    assert all(isinstance(g, bytes) and len(g) == 64 for g in gathered)
+    return b"".join(gathered)
+
+
 class Buffer:
     """One rank's endpoint.  ``group`` is any torch.distributed group (gloo or nccl);
     it is used once, to all-gather the 64-byte CUDA-IPC handles, and for barriers."""
@@ -115,9 +129,7 @@ class Buffer:
 
         h = (C.c_char * 64)()
         L.check(self.lib.b200ep_export_handle(self.ctx, h), "export_handle")
-        gathered: list = [None] * self.world
-        dist.all_gather_object(gathered, bytes(h.raw), group=self.group)
-        blob = b"".join(gathered)
+        blob = exchange_handles(self.group, bytes(h.raw))
         L.check(self.lib.b200ep_import_handles(self.ctx, blob, self.world), "import_handles")
         dist.barrier(group=self.group)
 

@@ -193,17 +193,35 @@ __device__ __forceinline__ float group_scale(float amax, bool ue8m0) {
   }
   return s;
 }
+// x / s rounded to nearest, without an IEEE division per element: r = RN(1/s) once per group,
+// q0 = x*r, e = fma(-q0, s, x) (exact residual), q = fma(e, r, q0)  (Markstein).  Equal to
+// __fdiv_rn(x, s) for every input that can reach a non-zero e4m3 code (tests/test_div_trick.py;
+// byte parity with vLLM's CUDA op is checked on the GPU in tests/test_gpu_layout_quant.py).
+__device__ __forceinline__ float div_by_scale(float x, float s, float r) {
+  const float q0 = __fmul_rn(x, r);
+  const float e = __fmaf_rn(-q0, s, x);
+  return __fmaf_rn(e, r, q0);
+}
 __device__ __forceinline__ uint2 quant8(const float (&f)[8], float s) {
+  const float r = __frcp_rn(s);
   uint32_t o[2];
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
-    float2 a = make_float2(__fdiv_rn(f[4 * i], s), __fdiv_rn(f[4 * i + 1], s));
-    float2 b = make_float2(__fdiv_rn(f[4 * i + 2], s), __fdiv_rn(f[4 * i + 3], s));
+    float2 a = make_float2(div_by_scale(f[4 * i], s, r), div_by_scale(f[4 * i + 1], s, r));
+    float2 b = make_float2(div_by_scale(f[4 * i + 2], s, r), div_by_scale(f[4 * i + 3], s, r));
     uint32_t lo = __nv_cvt_float2_to_fp8x2(a, __NV_SATFINITE, __NV_E4M3);
     uint32_t hi = __nv_cvt_float2_to_fp8x2(b, __NV_SATFINITE, __NV_E4M3);
     o[i] = lo | (hi << 16);
   }
   return make_uint2(o[0], o[1]);
+}
+// amax over the 16 lanes that hold one 128-element group
+__device__ __forceinline__ float group_amax16(float m) {
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+  return m;
 }
 
 #endif  // __CUDACC__

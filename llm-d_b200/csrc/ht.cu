@@ -105,36 +105,35 @@ struct HtDispatchArgs {
   int T, W, me, slot, e_local, ue8m0, ids_i64;
 };
 
-// Stage one token row in shared memory.  KIND: B200EP_X_* ; returns nothing, all lanes participate.
+constexpr int kRowThreads = 128;  // one CTA moves one row
+constexpr int kVpt = 8;           // 16-byte vectors in flight per thread (8 x 128 x 16 B = 16 KB per pass)
+
+// Stage one token row in shared memory with every load of the pass in flight at once.
+// KIND: B200EP_X_*; all threads of the CTA participate.
 template <int KIND>
-__device__ __forceinline__ void stage_row(const HtDispatchArgs& a, int t, char* s_row, float* s_scale, int lane) {
-  const int H = a.plan.H;
+__device__ __forceinline__ void stage_row(const HtDispatchArgs& a, int t, char* s_row, float* s_scale) {
+  const int H = a.plan.H, tid = threadIdx.x;
   if (KIND == B200EP_X_BF16_QUANT) {
-    // 16 lanes x 8 bf16 = one 128-element group; a warp covers two groups per step.
+    // 16 consecutive lanes x 8 bf16 = one 128-element group
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
     const int nvec = H / 8;
-    constexpr int U = 4;
-    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
-      int4 raw[U];
+    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
+      int4 raw[kVpt];
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
         raw[u] = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
+        if (v0 + u * kRowThreads >= nvec) break;  // uniform over the CTA
         float f[8];
         unpack8(raw[u], f);
-        float m = absmax8(f);
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-        const float s = group_scale(m, a.ue8m0 != 0);
+        const float s = group_scale(group_amax16(absmax8(f)), a.ue8m0 != 0);
         if (v < nvec) {
           *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
-          if ((lane & 15) == 0) s_scale[v >> 4] = s;
+          if ((tid & 15) == 0) s_scale[v >> 4] = s;
         }
       }
     }
@@ -142,93 +141,91 @@ __device__ __forceinline__ void stage_row(const HtDispatchArgs& a, int t, char* 
     const int row_bytes = a.plan.row_bytes;
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * row_bytes);
     const int nvec = row_bytes / 16;
-    constexpr int U = 4;
-    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
-      int4 raw[U];
+    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
+      int4 raw[kVpt];
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
         if (v < nvec) raw[u] = ld_nc_v4(src + v);
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
         if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
       }
     }
     if (KIND == B200EP_X_FP8) {
       const int ng = H / kGroup;
-      for (int g = lane; g < ng; g += 32) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+      for (int g = tid; g < ng; g += kRowThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
     }
   }
 }
 
+// One CTA per token (grid = T): the hardware block scheduler balances the rows over the SMs and
+// ~8 CTAs per SM keep >100 KB of loads in flight.  Warp 0 then fans the staged row out with one
+// TMA bulk copy per destination rank and writes the per-destination metadata.
 template <int KIND>
-__global__ void __launch_bounds__(512) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
+__global__ void __launch_bounds__(kRowThreads) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int W = a.W, K = a.plan.K;
   const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
-  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
-  char* s_row = s_mem + (size_t)warp * stage_bytes;
+  char* s_row = s_mem;
   float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+  const int t = blockIdx.x;
 
-  for (int t = blockIdx.x * nwarp + warp; t < a.T; t += gridDim.x * nwarp) {
-    // destination set of this token: lane d holds rank d's membership and row
-    int my_in = 0, my_row = -1;
-    if (lane < W) {
-      my_in = a.in_rank[(size_t)t * W + lane];
-      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
-    }
-    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
-    if (dmask == 0) continue;
-
-    bulk_wait_read0();  // my previous bulk copies have finished reading the stage
-    __syncwarp();
-    stage_row<KIND>(a, t, s_row, s_scale, lane);
+  // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
+  int my_in = 0, my_row = -1;
+  if (t < a.T && lane < W) {
+    my_in = a.in_rank[(size_t)t * W + lane];
+    if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
+  }
+  const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
+  if (dmask != 0) {  // uniform over the CTA
+    stage_row<KIND>(a, t, s_row, s_scale);
     fence_proxy_async_smem();
-    __syncwarp();
-    if (my_in) {
-      char* dst = a.peers.base[lane] + a.slot_off;
-      bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
-      if (scale_bytes) {
-        if ((scale_bytes & 15) == 0) {
+    __syncthreads();
+    if (warp == 0) {
+      if (my_in) {
+        char* dst = a.peers.base[lane] + a.slot_off;
+        bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
+        if (scale_bytes && (scale_bytes & 15) == 0)
           bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
+        bulk_commit();
+        *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+      }
+      if (scale_bytes && (scale_bytes & 15)) {  // scale vector not a 16-byte multiple: plain stores
+        const int ng = scale_bytes / 4;
+        for (int d = 0; d < W; ++d) {
+          if (!((dmask >> d) & 1u)) continue;
+          const int row = __shfl_sync(0xffffffffu, my_row, d);
+          float* dsts = reinterpret_cast<float*>(a.peers.base[d] + a.slot_off + a.plan.off_scales + (size_t)row * scale_bytes);
+          for (int g = lane; g < ng; g += 32) dsts[g] = s_scale[g];
         }
       }
-      bulk_commit();
-      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
-    }
-    if (scale_bytes && (scale_bytes & 15)) {  // rows whose scale vector is not a 16-byte multiple: plain stores
-      const int ng = scale_bytes / 4;
+    } else if (warp == 1) {
+      // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
+      long long id = -1;
+      float w = 0.f;
+      if (lane < K) {
+        id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
+                       : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
+        w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+      }
+      const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
       for (int d = 0; d < W; ++d) {
         if (!((dmask >> d) & 1u)) continue;
         const int row = __shfl_sync(0xffffffffu, my_row, d);
-        float* dsts = reinterpret_cast<float*>(a.peers.base[d] + a.slot_off + a.plan.off_scales + (size_t)row * scale_bytes);
-        for (int g = lane; g < ng; g += 32) dsts[g] = s_scale[g];
+        if (lane < K) {
+          char* dst = a.peers.base[d] + a.slot_off;
+          const bool mine = owner == d;
+          reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
+          reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
+        }
       }
     }
-    // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
-    long long id = -1;
-    float w = 0.f;
-    if (lane < K) {
-      id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
-                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
-      w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
-    }
-    const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
-    for (int d = 0; d < W; ++d) {
-      if (!((dmask >> d) & 1u)) continue;
-      const int row = __shfl_sync(0xffffffffu, my_row, d);
-      if (lane < K) {
-        char* dst = a.peers.base[d] + a.slot_off;
-        const bool mine = owner == d;
-        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
-        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
-      }
-    }
+    if (warp == 0) bulk_wait_all();
   }
-  bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
 }
 
@@ -252,49 +249,43 @@ struct HtCombineArgs {
   int T, W, me, slot;
 };
 
-// Expert rank: result row m goes back to (source rank, source token) = stage[t][me] on that rank.
-// Rows whose source is this rank are left where they are; the reduce reads dev_y directly.
-__global__ void __launch_bounds__(512) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
+// Expert rank, one CTA per received row: result row m goes back to (source rank, source token)
+// = stage[t][me] on that rank.  Rows whose source is this rank stay where they are; the reduce
+// reads dev_y directly.
+__global__ void __launch_bounds__(kRowThreads) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
   extern __shared__ __align__(128) char s_mem[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int tid = threadIdx.x;
   const int W = a.W;
-  const int row_bytes = 2 * a.plan.H;
-  char* s_row = s_mem + (size_t)warp * row_bytes;
+  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
+  const int m = blockIdx.x;
   const int M = a.meta->num_recv;
-  const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
-  const int nvec = row_bytes / 16;
-
-  for (int m = blockIdx.x * nwarp + warp; m < M; m += gridDim.x * nwarp) {
-    int s = 0;
-    while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
-    if (s == a.me) continue;
-    const int t = __ldcg(src_idx + m);
-    bulk_wait_read0();
-    __syncwarp();
+  int s = 0;
+  while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
+  if (m < M && s != a.me) {  // uniform over the CTA
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
-    constexpr int U = 4;
-    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
-      int4 raw[U];
+    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
+      int4 raw[kVpt];
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
         if (v < nvec) raw[u] = ld_nc_v4(src + v);
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
-        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
+      for (int u = 0; u < kVpt; ++u) {
+        const int v = v0 + u * kRowThreads + tid;
+        if (v < nvec) reinterpret_cast<int4*>(s_mem)[v] = raw[u];
       }
     }
     fence_proxy_async_smem();
-    __syncwarp();
-    if (lane == 0) {
-      char* dst = a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes;
-      bulk_s2g(dst, s_row, row_bytes);
+    __syncthreads();
+    if (tid == 0) {
+      const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+      const int t = __ldcg(src_idx + m);
+      bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_mem, row_bytes);
       bulk_commit();
+      bulk_wait_all();
     }
   }
-  bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtComb, a.slot, a.me);
 }
 
@@ -315,37 +306,64 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 }
 
 // Source rank: out[t] = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ).
-__global__ void __launch_bounds__(512) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
+// One warp per (token, 4 KB column block): 8 vectors per lane; the loads of up to four source rows
+// are in flight together (32 x 16 B per lane), accumulation order stays d = 0..W-1.
+constexpr int kRedVec = 4;
+__global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
   cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H;
   const int nvec = row_bytes / 16;
+  const int nblk = (nvec + 32 * kRedVec - 1) / (32 * kRedVec);
   const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
   const int my_first = a.meta->rank_prefix[a.me];
+  const long long items = (long long)a.T * nblk;
 
-  for (int t = blockIdx.x * nwarp + warp; t < a.T; t += gridDim.x * nwarp) {
+  for (long long it = (long long)blockIdx.x * nwarp + warp; it < items; it += (long long)gridDim.x * nwarp) {
+    const int t = (int)(it / nblk), v0 = (int)(it % nblk) * 32 * kRedVec;
     const char* rowp = nullptr;
     if (lane < W && a.in_rank[(size_t)t * W + lane]) {
       rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + a.send_off[(size_t)t * W + lane]) * row_bytes
                           : stage + ((size_t)t * W + lane) * row_bytes;
     }
     const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-    const char* rows[kMaxRanks];
+    float acc[kRedVec][8];
 #pragma unroll
-    for (int d = 0; d < kMaxRanks; ++d)
-      rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
+    for (int j = 0; j < kRedVec; ++j)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+#pragma unroll
+    for (int d0 = 0; d0 < kMaxRanks; d0 += 4) {
+      if ((dmask >> d0) == 0) break;
+      int4 raw[4][kRedVec];
+#pragma unroll
+      for (int dd = 0; dd < 4; ++dd) {
+        const char* rp = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d0 + dd));
+        if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+          for (int j = 0; j < kRedVec; ++j) {
+            const int v = v0 + j * 32 + lane;
+            if (v < nvec) raw[dd][j] = ld_cg_v4(rp + (size_t)v * 16);
+          }
+        }
+      }
+#pragma unroll
+      for (int dd = 0; dd < 4; ++dd) {
+        if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+          for (int j = 0; j < kRedVec; ++j) {
+            const int v = v0 + j * 32 + lane;
+            if (v < nvec) acc8(acc[j], raw[dd][j]);
+          }
+        }
+      }
+    }
     int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
-    for (int v = lane; v < nvec; v += 32) {
-      int4 raw[kMaxRanks];
 #pragma unroll
-      for (int d = 0; d < kMaxRanks; ++d)
-        if ((dmask >> d) & 1u) raw[d] = ld_cg_v4(rows[d] + (size_t)v * 16);
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int d = 0; d < kMaxRanks; ++d)
-        if ((dmask >> d) & 1u) acc8(acc, raw[d]);
-      st_na_v4(dst + v, pack8_bf16(acc));
+    for (int j = 0; j < kRedVec; ++j) {
+      const int v = v0 + j * 32 + lane;
+      if (v < nvec) st_na_v4(dst + v, pack8_bf16(acc[j]));
     }
   }
 }
@@ -457,15 +475,11 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.e_local = E / c->world;
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
-    const int stage_bytes = (plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
-    int warps = 100 * 1024 / stage_bytes;  // two CTAs per SM
-    if (warps > 12) warps = 12;
-    if (warps < 1) warps = 1;
-    const size_t smem = (size_t)warps * stage_bytes;
-    const int grid = grid_for(c, T, warps, 2);
+    const size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    const int grid = T > 0 ? T : 1;
     auto launch = [&](auto kern) -> int {
       B200EP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      kern<<<grid, warps * 32, smem, st>>>(a);
+      kern<<<grid, kRowThreads, smem, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
       return B200EP_OK;
     };
@@ -532,15 +546,11 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.epoch_ptr = &c->local->epoch[kFlagHtComb][slot];
   const int row_bytes = 2 * H;
   if (phases & B200EP_PHASE_SEND) {
-    int warps = 200 * 1024 / row_bytes;
-    if (warps > 16) warps = 16;
-    if (warps < 1) warps = 1;
-    const size_t smem = (size_t)warps * row_bytes;
-    // M lives on the device; size the grid for the worst case the host knows (mirror of the last notify)
+    // M lives on the device; the host mirror of the last notify gives the grid size
     const int M = c->host->num_recv[slot];
-    const int grid = grid_for(c, M, warps, 1);
+    const size_t smem = (size_t)row_bytes;
     B200EP_CUDA(cudaFuncSetAttribute(ht_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ht_combine_send_kernel<<<grid, warps * 32, smem, st>>>(a);
+    ht_combine_send_kernel<<<M > 0 ? M : 1, kRowThreads, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_PHASE_RECV) {
@@ -548,9 +558,9 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
       set_error("ht_combine: null pointer");
       return B200EP_ERR_ARG;
     }
-    const int warps = 16;
-    const int grid = grid_for(c, T, warps, 2);
-    ht_combine_recv_kernel<<<grid, warps * 32, 0, st>>>(a);
+    const int nblk = (row_bytes / 16 + 32 * kRedVec - 1) / (32 * kRedVec);
+    const int grid = grid_for(c, T * nblk, 8, 4);
+    ht_combine_recv_kernel<<<grid, 256, 0, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
