@@ -80,6 +80,15 @@ __device__ __forceinline__ uint64_t ld_acquire_sys_u64(const uint64_t* p) {
 __device__ __forceinline__ void st_release_sys_u64(uint64_t* p, uint64_t v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys_u64(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ unsigned atom_add_acq_rel_gpu(unsigned* p, unsigned v) {
+  unsigned r;
+  asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], %2;" : "=r"(r) : "l"(p), "r"(v) : "memory");
+  return r;
+}
 __device__ __forceinline__ uint64_t ld_acquire_gpu_u64(const uint64_t* p) {
   uint64_t v;
   asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -116,6 +125,8 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, uint32_t 
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all of this thread's groups have finished READING shared memory (buffer reusable)
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all but the most recent group have finished reading shared memory (double-buffered stages)
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 // all of this thread's groups are complete (writes performed)
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // order this thread's generic-proxy shared-memory writes before later async-proxy (TMA) reads
@@ -142,18 +153,35 @@ __device__ __forceinline__ void wait_flag_sys(const uint64_t* flag, uint64_t wan
 // counter: private device word, 0 before the kernel, reset to 0 by the last CTA.
 __device__ __forceinline__ void cta_done_then_signal(unsigned* counter, unsigned long long* epoch_ptr,
                                                      const Peers& peers, int world, int cat, int slot, int me) {
+  // A system-scope fence costs ~5 us on B200 (measured: an empty kernel whose CTAs each fence.sys),
+  // so exactly ONE is issued per kernel, by the last CTA.  Every other CTA releases its stores at
+  // gpu scope through the counter; the PTX memory model's causality order is transitive across
+  // scopes: stores -> bar.sync -> atom.acq_rel.gpu (CTA i) -> atom.acq_rel.gpu (last CTA)
+  // -> fence.acq_rel.sys -> st.relaxed.sys flag -> ld.acquire.sys on the peer.
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
-    unsigned prev = atomicAdd(counter, 1u);
+    const unsigned prev = atom_add_acq_rel_gpu(counter, 1u);
     if (prev == gridDim.x - 1) {
-      __threadfence_system();
       *counter = 0;
       const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
+      fence_acq_rel_sys();
       for (int d = 0; d < world; ++d)
-        st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[d] + flag_off(cat, slot, me)), epoch);
+        st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(peers.base[d] + flag_off(cat, slot, me)), epoch);
       *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
     }
+  }
+}
+
+// One CTA publishes to all peers: stores -> bar.sync -> (thread 0) one fence.acq_rel.sys -> W relaxed flags.
+__device__ __forceinline__ void single_cta_signal(unsigned long long* epoch_ptr, const Peers& peers, int world, int cat,
+                                                  int slot, int me) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
+    fence_acq_rel_sys();
+    for (int d = 0; d < world; ++d)
+      st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(peers.base[d] + flag_off(cat, slot, me)), epoch);
+    *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
   }
 }
 
@@ -185,7 +213,12 @@ __device__ __forceinline__ float absmax8(const float (&f)[8]) {
   return m;
 }
 __device__ __forceinline__ float group_scale(float amax, bool ue8m0) {
-  float s = __fdiv_rn(fmaxf(amax, 1e-10f), 448.0f);
+  // RN(max(amax, 1e-10) / 448) by Markstein's correction with the constant r = RN(1/448)
+  // (448 = 1.75 * 2^8: its significand is not all ones, so the corrected quotient is exact).
+  const float a = fmaxf(amax, 1e-10f);
+  const float r448 = 1.0f / 448.0f;  // folded at compile time, correctly rounded
+  const float q0 = __fmul_rn(a, r448);
+  float s = __fmaf_rn(__fmaf_rn(-q0, 448.0f, a), r448, q0);
   if (ue8m0) {  // 2^ceil(log2 max(s, 1e-10)), exact on the bit pattern (vLLM clamps the scale again here)
     uint32_t u = __float_as_uint(fmaxf(s, 1e-10f));
     u = (u & 0x7f800000u) + ((u & 0x007fffffu) ? 0x00800000u : 0u);
@@ -200,7 +233,7 @@ __device__ __forceinline__ float group_scale(float amax, bool ue8m0) {
 __device__ __forceinline__ float div_by_scale(float x, float s, float r) {
   const float q0 = __fmul_rn(x, r);
   const float e = __fmaf_rn(-q0, s, x);
-  return __fmaf_rn(e, r, q0);
+  return copysignf(__fmaf_rn(e, r, q0), x);  // keep the sign of a zero quotient, as the division does
 }
 __device__ __forceinline__ uint2 quant8(const float (&f)[8], float s) {
   const float r = __frcp_rn(s);

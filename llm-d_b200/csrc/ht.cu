@@ -32,8 +32,6 @@ namespace b200ep {
 __global__ void __launch_bounds__(256)
     ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, const int32_t* __restrict__ tok_per_rank,
                           const int32_t* __restrict__ tok_per_expert, unsigned long long* epoch_ptr) {
-  __shared__ unsigned long long s_epoch;
-  if (threadIdx.x == 0) s_epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
   for (int d = 0; d < W; ++d) {
     char* ctrl = peers.base[d];
     int32_t* cr = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntRankOff) + ((size_t)slot * kMaxRanks + me) * kMaxRanks;
@@ -41,12 +39,7 @@ __global__ void __launch_bounds__(256)
     if ((int)threadIdx.x < W) cr[threadIdx.x] = tok_per_rank[threadIdx.x];
     for (int i = threadIdx.x; i < e_local; i += blockDim.x) ce[i] = tok_per_expert[d * e_local + i];
   }
-  __syncthreads();
-  if ((int)threadIdx.x < W) {
-    __threadfence_system();
-    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[threadIdx.x] + flag_off(kFlagHtNotify, slot, me)), s_epoch);
-  }
-  if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = s_epoch;
+  single_cta_signal(epoch_ptr, peers, W, kFlagHtNotify, slot, me);
 }
 
 __global__ void __launch_bounds__(256)
@@ -102,98 +95,106 @@ struct HtDispatchArgs {
   unsigned* done;
   size_t slot_off;  // kCtrlBytes + slot * slot_bytes
   unsigned long long* epoch_ptr;
-  int T, W, me, slot, e_local, ue8m0, ids_i64;
+  int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
 };
 
-constexpr int kRowThreads = 128;  // one CTA moves one row
-constexpr int kVpt = 8;           // 16-byte vectors in flight per thread (8 x 128 x 16 B = 16 KB per pass)
+constexpr int kTeamThreads = 128;  // a team of 4 warps moves one row at a time
+constexpr int kTeams = 4;          // teams per CTA (512 threads); one sys-scope fence per CTA at the end
+constexpr int kVpt = 8;            // 16-byte vectors in flight per thread (8 x 128 x 16 B = 16 KB per pass)
 
-// Stage one token row in shared memory with every load of the pass in flight at once.
-// KIND: B200EP_X_*; all threads of the CTA participate.
+__device__ __forceinline__ void team_bar(int team) {
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + team), "r"(kTeamThreads) : "memory");
+}
+
+// Load one pass of a row into registers (all loads in flight), nothing else.
+__device__ __forceinline__ void load_pass(const int4* src, int nvec, int v0, int ttid, int4 (&raw)[kVpt]) {
+#pragma unroll
+  for (int u = 0; u < kVpt; ++u) {
+    const int v = v0 + u * kTeamThreads + ttid;
+    raw[u] = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
+  }
+}
+
+// Registers -> shared-memory stage; KIND B200EP_X_BF16_QUANT quantises on the way
+// (16 consecutive lanes x 8 bf16 = one 128-element group).
 template <int KIND>
-__device__ __forceinline__ void stage_row(const HtDispatchArgs& a, int t, char* s_row, float* s_scale) {
-  const int H = a.plan.H, tid = threadIdx.x;
-  if (KIND == B200EP_X_BF16_QUANT) {
-    // 16 consecutive lanes x 8 bf16 = one 128-element group
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
-    const int nvec = H / 8;
-    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
-      int4 raw[kVpt];
+__device__ __forceinline__ void store_pass(const int4 (&raw)[kVpt], int nvec, int v0, int ttid, char* s_row,
+                                           float* s_scale, bool ue8m0) {
 #pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        raw[u] = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
+  for (int u = 0; u < kVpt; ++u) {
+    const int v = v0 + u * kTeamThreads + ttid;
+    if (v0 + u * kTeamThreads >= nvec) break;  // uniform over the team
+    if (KIND == B200EP_X_BF16_QUANT) {
+      float f[8];
+      unpack8(raw[u], f);
+      const float s = group_scale(group_amax16(absmax8(f)), ue8m0);
+      if (v < nvec) {
+        *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
+        if ((ttid & 15) == 0) s_scale[v >> 4] = s;
       }
-#pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        if (v0 + u * kRowThreads >= nvec) break;  // uniform over the CTA
-        float f[8];
-        unpack8(raw[u], f);
-        const float s = group_scale(group_amax16(absmax8(f)), a.ue8m0 != 0);
-        if (v < nvec) {
-          *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
-          if ((tid & 15) == 0) s_scale[v >> 4] = s;
-        }
-      }
-    }
-  } else {
-    const int row_bytes = a.plan.row_bytes;
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * row_bytes);
-    const int nvec = row_bytes / 16;
-    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
-      int4 raw[kVpt];
-#pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        if (v < nvec) raw[u] = ld_nc_v4(src + v);
-      }
-#pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
-      }
-    }
-    if (KIND == B200EP_X_FP8) {
-      const int ng = H / kGroup;
-      for (int g = tid; g < ng; g += kRowThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+    } else {
+      if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
     }
   }
 }
 
-// One CTA per token (grid = T): the hardware block scheduler balances the rows over the SMs and
-// ~8 CTAs per SM keep >100 KB of loads in flight.  Warp 0 then fans the staged row out with one
-// TMA bulk copy per destination rank and writes the per-destination metadata.
+// Persistent CTAs of four 128-thread teams.  Per row a team: issues every load of the row (up to
+// 16 KB in flight), waits until its previous TMA bulk copies have read the stage, quantises into
+// the stage, and warp 0 fans the row out with ONE cp.async.bulk per destination rank while warp 1
+// writes the per-destination metadata.  The next row's loads overlap the bulk copies of this one.
 template <int KIND>
-__global__ void __launch_bounds__(kRowThreads) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int W = a.W, K = a.plan.K;
+  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
+  const int lane = tid & 31, twarp = ttid >> 5;
+  const int W = a.W, K = a.plan.K, H = a.plan.H;
   const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
-  char* s_row = s_mem;
-  float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
-  const int t = blockIdx.x;
+  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
+  char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
+  const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
+  const int nvec = in_row_bytes / 16;
+  int n = 0;  // rows this team has staged so far: stage = n % nstage, one bulk group per row and lane
 
-  // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
-  int my_in = 0, my_row = -1;
-  if (t < a.T && lane < W) {
-    my_in = a.in_rank[(size_t)t * W + lane];
-    if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
-  }
-  const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
-  if (dmask != 0) {  // uniform over the CTA
-    stage_row<KIND>(a, t, s_row, s_scale);
+  for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
+    // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
+    int my_in = 0, my_row = -1;
+    if (lane < W) {
+      my_in = a.in_rank[(size_t)t * W + lane];
+      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
+    }
+    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
+    if (dmask == 0) continue;  // uniform over the team
+
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
+    int4 raw[kVpt];
+    load_pass(src, nvec, 0, ttid, raw);
+    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
+    float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+    ++n;
+    if (twarp == 0) {  // the bulk copies that last used this stage have finished reading it
+      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+    }
+    team_bar(team);
+    store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
+    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {  // rows wider than 16 KB
+      load_pass(src, nvec, v0, ttid, raw);
+      store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
+    }
+    if (KIND == B200EP_X_FP8) {
+      const int ng = H / kGroup;
+      for (int g = ttid; g < ng; g += kTeamThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+    }
     fence_proxy_async_smem();
-    __syncthreads();
-    if (warp == 0) {
+    team_bar(team);
+    if (twarp == 0) {
       if (my_in) {
         char* dst = a.peers.base[lane] + a.slot_off;
         bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
         if (scale_bytes && (scale_bytes & 15) == 0)
           bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
-        bulk_commit();
         *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
       }
+      bulk_commit();  // every lane, every row (possibly empty): group count == rows staged
       if (scale_bytes && (scale_bytes & 15)) {  // scale vector not a 16-byte multiple: plain stores
         const int ng = scale_bytes / 4;
         for (int d = 0; d < W; ++d) {
@@ -202,8 +203,9 @@ __global__ void __launch_bounds__(kRowThreads) ht_dispatch_send_kernel(const __g
           float* dsts = reinterpret_cast<float*>(a.peers.base[d] + a.slot_off + a.plan.off_scales + (size_t)row * scale_bytes);
           for (int g = lane; g < ng; g += 32) dsts[g] = s_scale[g];
         }
+        __syncwarp();
       }
-    } else if (warp == 1) {
+    } else if (twarp == 1) {
       // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
       long long id = -1;
       float w = 0.f;
@@ -224,8 +226,8 @@ __global__ void __launch_bounds__(kRowThreads) ht_dispatch_send_kernel(const __g
         }
       }
     }
-    if (warp == 0) bulk_wait_all();
   }
+  if ((ttid >> 5) == 0) bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
 }
 
@@ -246,46 +248,50 @@ struct HtCombineArgs {
   unsigned* done;
   size_t slot_off;
   unsigned long long* epoch_ptr;
-  int T, W, me, slot;
+  int T, W, me, slot, nstage;
 };
 
-// Expert rank, one CTA per received row: result row m goes back to (source rank, source token)
-// = stage[t][me] on that rank.  Rows whose source is this rank stay where they are; the reduce
-// reads dev_y directly.
-__global__ void __launch_bounds__(kRowThreads) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
+// Expert rank: result row m goes back to (source rank, source token) = stage[t][me] on that rank.
+// Rows whose source is this rank stay where they are; the reduce reads dev_y directly.
+// Same team structure as the dispatch: loads of the next row overlap the bulk copy of this one.
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
   extern __shared__ __align__(128) char s_mem[];
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  const int m = blockIdx.x;
+  char* s_team = s_mem + (size_t)team * a.nstage * row_bytes;
+  int n = 0;
   const int M = a.meta->num_recv;
-  int s = 0;
-  while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
-  if (m < M && s != a.me) {  // uniform over the CTA
+  const int my_lo = a.meta->rank_prefix[a.me], my_hi = a.meta->rank_prefix[a.me + 1];
+  const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+
+  for (int m = blockIdx.x * kTeams + team; m < M; m += gridDim.x * kTeams) {
+    if (m >= my_lo && m < my_hi) continue;  // uniform over the team
+    int s = 0;
+    while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
-    for (int v0 = 0; v0 < nvec; v0 += kRowThreads * kVpt) {
-      int4 raw[kVpt];
-#pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        if (v < nvec) raw[u] = ld_nc_v4(src + v);
-      }
-#pragma unroll
-      for (int u = 0; u < kVpt; ++u) {
-        const int v = v0 + u * kRowThreads + tid;
-        if (v < nvec) reinterpret_cast<int4*>(s_mem)[v] = raw[u];
-      }
+    int4 raw[kVpt];
+    load_pass(src, nvec, 0, ttid, raw);
+    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * row_bytes;
+    ++n;
+    if (ttid == 0) {
+      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+    }
+    team_bar(team);
+    store_pass<B200EP_X_BF16>(raw, nvec, 0, ttid, s_row, nullptr, false);
+    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
+      load_pass(src, nvec, v0, ttid, raw);
+      store_pass<B200EP_X_BF16>(raw, nvec, v0, ttid, s_row, nullptr, false);
     }
     fence_proxy_async_smem();
-    __syncthreads();
-    if (tid == 0) {
-      const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+    team_bar(team);
+    if (ttid == 0) {
       const int t = __ldcg(src_idx + m);
-      bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_mem, row_bytes);
+      bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_row, row_bytes);
       bulk_commit();
-      bulk_wait_all();
     }
   }
+  if (ttid == 0) bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtComb, a.slot, a.me);
 }
 
@@ -306,8 +312,9 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 }
 
 // Source rank: out[t] = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ).
-// One warp per (token, 4 KB column block): 8 vectors per lane; the loads of up to four source rows
-// are in flight together (32 x 16 B per lane), accumulation order stays d = 0..W-1.
+// One warp per (token, half row); the row pointers are resolved once per item, then the warp walks
+// the half row in batches of 4 vectors per lane with the loads of up to four source rows in flight
+// together (16 x 16 B per lane).  Accumulation order stays d = 0..W-1.
 constexpr int kRedVec = 4;
 __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
   cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
@@ -315,55 +322,62 @@ __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_co
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H;
   const int nvec = row_bytes / 16;
-  const int nblk = (nvec + 32 * kRedVec - 1) / (32 * kRedVec);
+  const int nsplit = nvec >= 256 ? 2 : 1;
+  const int per = (nvec / nsplit + 31) / 32 * 32;  // vectors per item, multiple of 32
   const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
   const int my_first = a.meta->rank_prefix[a.me];
-  const long long items = (long long)a.T * nblk;
+  const long long items = (long long)a.T * nsplit;
 
   for (long long it = (long long)blockIdx.x * nwarp + warp; it < items; it += (long long)gridDim.x * nwarp) {
-    const int t = (int)(it / nblk), v0 = (int)(it % nblk) * 32 * kRedVec;
+    const int t = (int)(it / nsplit), vbeg = (int)(it % nsplit) * per;
+    const int vend = min(nvec, vbeg + per);
     const char* rowp = nullptr;
     if (lane < W && a.in_rank[(size_t)t * W + lane]) {
       rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + a.send_off[(size_t)t * W + lane]) * row_bytes
                           : stage + ((size_t)t * W + lane) * row_bytes;
     }
     const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-    float acc[kRedVec][8];
+    const char* rows[kMaxRanks];
 #pragma unroll
-    for (int j = 0; j < kRedVec; ++j)
-#pragma unroll
-      for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
-#pragma unroll
-    for (int d0 = 0; d0 < kMaxRanks; d0 += 4) {
-      if ((dmask >> d0) == 0) break;
-      int4 raw[4][kRedVec];
-#pragma unroll
-      for (int dd = 0; dd < 4; ++dd) {
-        const char* rp = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d0 + dd));
-        if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-          for (int j = 0; j < kRedVec; ++j) {
-            const int v = v0 + j * 32 + lane;
-            if (v < nvec) raw[dd][j] = ld_cg_v4(rp + (size_t)v * 16);
-          }
-        }
-      }
-#pragma unroll
-      for (int dd = 0; dd < 4; ++dd) {
-        if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-          for (int j = 0; j < kRedVec; ++j) {
-            const int v = v0 + j * 32 + lane;
-            if (v < nvec) acc8(acc[j], raw[dd][j]);
-          }
-        }
-      }
-    }
+    for (int d = 0; d < kMaxRanks; ++d)
+      rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
     int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
+    for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
+      float acc[kRedVec][8];
 #pragma unroll
-    for (int j = 0; j < kRedVec; ++j) {
-      const int v = v0 + j * 32 + lane;
-      if (v < nvec) st_na_v4(dst + v, pack8_bf16(acc[j]));
+      for (int j = 0; j < kRedVec; ++j)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+#pragma unroll
+      for (int d0 = 0; d0 < kMaxRanks; d0 += 4) {
+        if ((dmask >> d0) == 0) break;
+        int4 raw[4][kRedVec];
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd) {
+          if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+            for (int j = 0; j < kRedVec; ++j) {
+              const int v = v0 + j * 32 + lane;
+              if (v < vend) raw[dd][j] = ld_cg_v4(rows[d0 + dd] + (size_t)v * 16);
+            }
+          }
+        }
+#pragma unroll
+        for (int dd = 0; dd < 4; ++dd) {
+          if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+            for (int j = 0; j < kRedVec; ++j) {
+              const int v = v0 + j * 32 + lane;
+              if (v < vend) acc8(acc[j], raw[dd][j]);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < kRedVec; ++j) {
+        const int v = v0 + j * 32 + lane;
+        if (v < vend) st_na_v4(dst + v, pack8_bf16(acc[j]));
+      }
     }
   }
 }
@@ -475,11 +489,13 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.e_local = E / c->world;
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
-    const size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
-    const int grid = T > 0 ? T : 1;
+    const size_t stage_bytes = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    a.nstage = 2 * kTeams * stage_bytes <= 100 * 1024 ? 2 : 1;  // two CTAs per SM must still fit
+    const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
+    const int grid = grid_for(c, T, kTeams, 2);
     auto launch = [&](auto kern) -> int {
       B200EP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      kern<<<grid, kRowThreads, smem, st>>>(a);
+      kern<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
       return B200EP_OK;
     };
@@ -548,9 +564,15 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   if (phases & B200EP_PHASE_SEND) {
     // M lives on the device; the host mirror of the last notify gives the grid size
     const int M = c->host->num_recv[slot];
-    const size_t smem = (size_t)row_bytes;
+    a.nstage = 2 * (size_t)kTeams * row_bytes <= 100 * 1024 ? 2 : 1;
+    int ctas_per_sm = 2;
+    if (a.nstage == 1 && 2 * (size_t)kTeams * row_bytes <= 200 * 1024) {  // wide rows: one CTA per SM, still two stages
+      a.nstage = 2;
+      ctas_per_sm = 1;
+    }
+    const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
     B200EP_CUDA(cudaFuncSetAttribute(ht_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ht_combine_send_kernel<<<M > 0 ? M : 1, kRowThreads, smem, st>>>(a);
+    ht_combine_send_kernel<<<grid_for(c, M, kTeams, ctas_per_sm), kTeams * kTeamThreads, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_PHASE_RECV) {
@@ -558,8 +580,8 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
       set_error("ht_combine: null pointer");
       return B200EP_ERR_ARG;
     }
-    const int nblk = (row_bytes / 16 + 32 * kRedVec - 1) / (32 * kRedVec);
-    const int grid = grid_for(c, T * nblk, 8, 4);
+    const int nsplit = row_bytes / 16 >= 256 ? 2 : 1;
+    const int grid = grid_for(c, T * nsplit, 8, 2);
     ht_combine_recv_kernel<<<grid, 256, 0, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }

@@ -70,14 +70,7 @@ __global__ void __launch_bounds__(1024)
     int32_t* ce = reinterpret_cast<int32_t*>(peers.base[d] + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + me) * kLlMaxExperts;
     for (int i = tid; i < E; i += blockDim.x) ce[i] = sc->cnt_mine[i];
   }
-  __syncthreads();
-  const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
-  if (tid < W) {
-    __threadfence_system();
-    st_release_sys_u64(reinterpret_cast<uint64_t*>(peers.base[tid] + flag_off(kFlagLlCount, slot, me)), epoch);
-  }
-  __syncthreads();
-  if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
+  single_cta_signal(epoch_ptr, peers, W, kFlagLlCount, slot, me);
 }
 
 struct LlDispatchArgs {

@@ -40,8 +40,13 @@ def test_markstein_division_matches_ieee_for_bf16_inputs():
     xs = ((xs.view(np.uint32) >> 16) << 16).view(np.float32)  # truncate to a bf16 value <= amax
     xs[::7] = amax[::7]  # the element that defines amax
     bad = 0
+    r448 = rn32(Fraction(1, 448))
     for a, x in zip(amax.tolist(), xs.tolist()):
         s = rn32(Fraction(a) / 448)
+        # the kernel derives the scale the same way: q0 = a*r448, s = fma(fma(-q0, 448, a), r448, q0)
+        s0 = rn32(Fraction(a) * Fraction(r448))
+        es = rn32(Fraction(a) - Fraction(s0) * 448)
+        assert rn32(Fraction(s0) + Fraction(es) * Fraction(r448)) == s
         r = rn32(1 / Fraction(s))
         q0 = rn32(Fraction(x) * Fraction(r))
         e = rn32(Fraction(x) - Fraction(q0) * Fraction(s))
