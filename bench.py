@@ -61,47 +61,61 @@ def make_inputs(seed: int, tokens: int = T):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (profiling recipe)."""
+    """SM clock and throttle reasons sampled DURING the timed region (profiling recipe), through NVML
+    in a background thread.  (A looping `nvidia-smi -lms` process was tried first: its queries stalled
+    rank 0's kernel launches by ~1 ms per step at N=4, so every other rank waited in the count exchange.)"""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    def __init__(self, index: int, period_s: float = 0.02):
+        self.index, self.period, self.samples, self.stop_flag, self.thread = index, period_s, [], False, None
+        self.mx = None
+        try:
+            import pynvml
 
-    def __init__(self, index: int):
-        self.index, self.lines, self.proc = index, [], None
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def _one(self):
+        nv = self.nv
+        return (float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)),
+                int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons")
+                else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)))
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                self.samples.append(self._one())
+            except Exception:
+                pass
+            time.sleep(self.period)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._pump, daemon=True).start()
-        except Exception:
-            self.proc = None
-
-    def _pump(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+        if self.nv is None:
+            return
+        self.samples.append(self._one())
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            p = [q.strip() for q in ln.split(",")]
-            if len(p) < 6:
-                continue
-            try:
-                sm.append(float(p[0])); mx = float(p[1])
-            except ValueError:
-                continue
-            for n, v in zip(names, p[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
+        self.stop_flag = True
+        self.thread.join(timeout=1.0)
+        try:
+            self.samples.append(self._one())
+        except Exception:
+            pass
+        sm = sorted(s for s, _ in self.samples)
+        bits = 0
+        for _, r in self.samples:
+            bits |= r
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake_slowdown"}
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.mx,
+                "reasons": sorted(n for b, n in names.items() if bits & b), "samples": len(sm), "how": "NVML, 20 ms period"}
 
 
 def cpu_baseline(sample_tokens: int, repeats: int, threads: int | None = None):
@@ -169,6 +183,7 @@ def main():
     ap.add_argument("--no-ll", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sym-gb", type=float, default=0.0)
+    ap.add_argument("--breakdown", action="store_true", help="per-phase CUDA-event breakdown of the step (stderr)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -214,15 +229,29 @@ def main():
     remote_copies = []
     last = {}
 
+    marks = []
+
     def step(i, timed):
         b = i % NBUF
+        if args.breakdown and timed:
+            m = [ev() for _ in range(5)]
+            th0 = time.perf_counter()
+            m[0].record()
         lay = buf.get_dispatch_layout(idss[b], E)
         h, a = buf._dispatch_prepare(xs[b], idss[b], wss[b], E, None, True, False, lay)
         buf.ht_notify(h.slot, lay)
+        if args.breakdown and timed:
+            m[1].record(); th1 = time.perf_counter()
         buf._dispatch_after_notify(h)
+        if args.breakdown and timed:
+            th2 = time.perf_counter(); m[2].record()
         buf.ht_dispatch_launch(h, *a, L.PHASE_ALL)
+        if args.breakdown and timed:
+            m[3].record()
         y = y_pool[: h.num_recv]
         buf.combine(y, h, out)
+        if args.breakdown and timed:
+            m[4].record(); marks.append((m, th1 - th0, th2 - th1))
         last["h"], last["a"], last["y"] = h, a, y
         if timed:
             remote_copies.append(h.num_recv - (h.rank_prefix[rank + 1] - h.rank_prefix[rank]))
@@ -273,6 +302,12 @@ def main():
     torch.cuda.synchronize()
     barrier()
     del flush
+    if args.breakdown:
+        n = len(marks)
+        seg = [sum(m[j].elapsed_time(m[j + 1]) for m, _, _ in marks) / n * 1e3 for j in range(4)]
+        print(f"[rank {rank}] step breakdown us: layout+notify(gpu) {seg[0]:.1f} | host wait gap {seg[1]:.1f} | dispatch {seg[2]:.1f} "
+              f"| combine {seg[3]:.1f} || host launch {sum(a for _, a, _ in marks) / n * 1e6:.1f} host wait {sum(b for _, _, b in marks) / n * 1e6:.1f}",
+              file=sys.stderr, flush=True)
     d_ms = sorted(p.elapsed_time(q) for p, q in k_disp)
     c_ms = sorted(p.elapsed_time(q) for p, q in k_comb)
     d_avg, c_avg = sum(d_ms) / len(d_ms), sum(c_ms) / len(c_ms)

@@ -261,14 +261,22 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_combine_send_kerne
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
   char* s_team = s_mem + (size_t)team * a.nstage * row_bytes;
   int n = 0;
-  const int M = a.meta->num_recv;
-  const int my_lo = a.meta->rank_prefix[a.me], my_hi = a.meta->rank_prefix[a.me + 1];
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  // Work order: consecutive items go to DIFFERENT source ranks, starting at rank me+1, so that at
+  // any moment the W ranks push along a permutation instead of all converging on rank 0 (incast).
+  int maxlen = 0;
+  for (int k = 1; k < W; ++k) {
+    const int s = (a.me + k) % W;
+    maxlen = max(maxlen, a.meta->rank_prefix[s + 1] - a.meta->rank_prefix[s]);
+  }
+  const long long items = (long long)maxlen * (W - 1);
 
-  for (int m = blockIdx.x * kTeams + team; m < M; m += gridDim.x * kTeams) {
-    if (m >= my_lo && m < my_hi) continue;  // uniform over the team
-    int s = 0;
-    while (s + 1 < W && m >= a.meta->rank_prefix[s + 1]) ++s;
+  for (long long i = (long long)blockIdx.x * kTeams + team; i < items; i += (long long)gridDim.x * kTeams) {
+    const int s = (a.me + 1 + (int)(i % (W - 1))) % W;
+    const int v = (int)(i / (W - 1));
+    const int lo = a.meta->rank_prefix[s];
+    if (v >= a.meta->rank_prefix[s + 1] - lo) continue;  // uniform over the team
+    const int m = lo + v;
     const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
     int4 raw[kVpt];
     load_pass(src, nvec, 0, ttid, raw);
