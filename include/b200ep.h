@@ -109,6 +109,23 @@ int b200ep_layout(b200ep_ctx* ctx, const void* dev_topk_ids, int ids_i64, int T,
                   int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
                   uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream);
 
+/* Same outputs as b200ep_layout, but no context and NO device allocation anywhere on the path.
+ * This entry point has no counterpart in the reference (DeepEP's layout always runs on a Buffer).
+ * It exists for callers that cannot allocate when they need a layout: a serving worker whose
+ * remaining GPU memory already belongs to its KV-cache pool (a late cudaMalloc fails or shrinks
+ * the pool's headroom), and tools/tests that only want counts and offsets and have no reason to
+ * create a context (b200ep_create allocates gigabytes).  The kernel's scratch is a fixed array
+ * inside the library (about 16 KB on every GPU that loads it, until the process exits), hence:
+ *   - T <= 65536 tokens per call; more is rejected with B200EP_ERR_CAPACITY;
+ *   - all calls on a device share that array and each call clears it first, so calls whose
+ *     kernels overlap on the GPU race: serialise them (one stream, or external ordering);
+ *   - the first call on a device resolves the array's address before launching; make that
+ *     first call before any stream capture begins.
+ * `world` is the number of ranks the experts are sharded over (1..B200EP_MAX_RANKS). */
+int b200ep_layout_noalloc(int world, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
+                          int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
+                          uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream);
+
 /* ------------------------------------------------- fp8 quantiser (stand-alone) */
 
 /* Same arithmetic as vLLM per_token_group_quant_fp8 with group 128

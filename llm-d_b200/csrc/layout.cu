@@ -188,3 +188,190 @@ extern "C" int b200ep_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i6
   B200EP_CUDA(cudaGetLastError());
   return B200EP_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the layout kernel (entry point b200ep_layout_noalloc).
+//
+// b200ep_layout needs a context, and b200ep_create allocates (the symmetric region alone is
+// gigabytes).  Some callers cannot allocate device memory at the point where they need a routing
+// layout: a vLLM worker that has already handed the rest of the GPU to its KV-cache pool (a late
+// cudaMalloc there fails with out-of-memory or eats into the pool's headroom), and small tools or
+// tests that only want counts and offsets for a batch of top-k ids and have no reason to set up a
+// communication context.  For them the scratch this kernel needs -- the block ticket and the
+// per-block totals that blocks publish to each other -- lives in the fixed array below.
+//
+// Limits and sharing, for users of this entry point:
+//   * at most kNoAllocMaxTokens tokens per call (the array has one row per 256-token block);
+//     larger batches are rejected, use b200ep_layout for those;
+//   * every GPU that loads libb200ep.so carries the array (about 16 KB) until the process exits;
+//   * all calls on a device share the one array and each call begins by clearing it on the
+//     caller's stream, so two calls whose kernels overlap on the GPU (different streams, or
+//     different host threads) race with each other: serialise them;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress)
+//     before it launches anything; make that first call before any stream capture begins.
+// No cudaMalloc / cudaFree / allocating library routine is called here.
+namespace b200ep {
+
+constexpr int kNoAllocMaxTokens = 65536;
+constexpr int kNoAllocMaxBlocks = kNoAllocMaxTokens / 256;
+constexpr int kNoAllocMaxDevices = 64;
+
+struct LayoutStaticScratch {
+  unsigned long long ticket;                             // next logical block id; cleared per call
+  unsigned long long pad[31];
+  unsigned long long pub[kNoAllocMaxBlocks][kMaxRanks];  // (1 << 32 | count) once published, 0 before
+};
+
+// In host code this name is only a stand-in for the symbol; the device address is obtained once
+// per device with cudaGetSymbolAddress and handed to the kernel as an ordinary pointer.
+static __device__ __align__(256) unsigned char g_layout_static_scratch[sizeof(LayoutStaticScratch)];
+
+template <typename IdT>
+__global__ void __launch_bounds__(256)
+    layout_noalloc_kernel(const IdT* __restrict__ ids, int T, int K, int E, int W, int e_local,
+                          int32_t* __restrict__ tok_per_rank, int32_t* __restrict__ tok_per_expert,
+                          uint8_t* __restrict__ in_rank, int32_t* __restrict__ send_off, LayoutStaticScratch* sc) {
+  extern __shared__ int s_hist[];  // [E]
+  __shared__ int s_warp_tot[8][kMaxRanks];
+  __shared__ int s_total[kMaxRanks];
+  __shared__ int s_base[kMaxRanks];
+  __shared__ unsigned s_bid;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_bid = (unsigned)atomicAdd(&sc->ticket, 1ull);
+  for (int e = tid; e < E; e += 256) s_hist[e] = 0;
+  if (tid < kMaxRanks) s_base[tid] = 0;
+  __syncthreads();
+  const int bid = (int)s_bid;
+  const int t = bid * 256 + tid;
+
+  unsigned mask = 0;
+  if (t < T) {
+    const IdT* row = ids + (size_t)t * K;
+    for (int k = 0; k < K; ++k) {
+      long long id = (long long)row[k];
+      if (id >= 0 && id < E) {
+        atomicAdd(&s_hist[(int)id], 1);
+        mask |= 1u << ((int)id / e_local);
+      }
+    }
+  }
+  int loc[kMaxRanks];
+#pragma unroll
+  for (int d = 0; d < kMaxRanks; ++d) {
+    if (d < W) {
+      unsigned ball = __ballot_sync(0xffffffffu, (mask >> d) & 1u);
+      loc[d] = __popc(ball & ((1u << lane) - 1u));
+      if (lane == 0) s_warp_tot[warp][d] = __popc(ball);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int d = 0; d < kMaxRanks; ++d) {
+    if (d < W)
+      for (int w = 0; w < warp; ++w) loc[d] += s_warp_tot[w][d];
+  }
+  if (tid < W) {
+    int s = 0;
+    for (int w = 0; w < 8; ++w) s += s_warp_tot[w][tid];
+    s_total[tid] = s;
+    st_release_gpu_u64(reinterpret_cast<uint64_t*>(&sc->pub[bid][tid]), (1ull << 32) | (uint32_t)s);
+  }
+  int part[kMaxRanks];
+#pragma unroll
+  for (int d = 0; d < kMaxRanks; ++d) part[d] = 0;
+  for (int b = tid; b < bid; b += 256) {
+#pragma unroll
+    for (int d = 0; d < kMaxRanks; ++d) {
+      if (d < W) {
+        uint64_t v;
+        do {
+          v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(&sc->pub[b][d]));
+        } while ((v >> 32) == 0);
+        part[d] += (int)(uint32_t)v;
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < kMaxRanks; ++d)
+    if (d < W && part[d]) atomicAdd(&s_base[d], part[d]);
+  __syncthreads();
+  if (t < T) {
+#pragma unroll
+    for (int d = 0; d < kMaxRanks; ++d) {
+      if (d < W) {
+        in_rank[(size_t)t * W + d] = (mask >> d) & 1u;
+        send_off[(size_t)t * W + d] = ((mask >> d) & 1u) ? s_base[d] + loc[d] : -1;
+      }
+    }
+  }
+  if (bid == (int)gridDim.x - 1 && tid < W) tok_per_rank[tid] = s_base[tid] + s_total[tid];
+  for (int e = tid; e < E; e += 256) {
+    int h = s_hist[e];
+    if (h) atomicAdd(&tok_per_expert[e], h);
+  }
+}
+
+}  // namespace b200ep
+
+#include <mutex>
+
+extern "C" int b200ep_layout_noalloc(int world, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
+                                     int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
+                                     uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream) {
+  if (world < 1 || world > kMaxRanks || T < 0 || K <= 0 || K > kMaxTopk || E <= 0 || E % world != 0 ||
+      E / world > kMaxLocalExperts) {
+    set_error("layout_noalloc: bad shape T=%d K=%d E=%d world=%d", T, K, E, world);
+    return B200EP_ERR_ARG;
+  }
+  if (T > kNoAllocMaxTokens) {
+    set_error("layout_noalloc: T=%d is more than the %d tokens the fixed scratch array of this entry point covers; "
+              "use b200ep_layout (which owns per-context scratch) for larger batches",
+              T, kNoAllocMaxTokens);
+    return B200EP_ERR_CAPACITY;
+  }
+  if (!dev_tokens_per_rank || !dev_tokens_per_expert || (T > 0 && (!dev_topk_ids || !dev_is_token_in_rank || !dev_send_off))) {
+    set_error("layout_noalloc: null pointer");
+    return B200EP_ERR_ARG;
+  }
+  // Set-up, once per device, with that device current: resolve the array's device address.
+  static std::mutex mu;
+  static LayoutStaticScratch* scratch_of[kNoAllocMaxDevices] = {};
+  int dev = -1;
+  B200EP_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    set_error("layout_noalloc: device ordinal %d out of range", dev);
+    return B200EP_ERR_ARG;
+  }
+  LayoutStaticScratch* sc = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!scratch_of[dev]) {
+      void* p = nullptr;
+      B200EP_CUDA(cudaGetSymbolAddress(&p, g_layout_static_scratch));
+      scratch_of[dev] = reinterpret_cast<LayoutStaticScratch*>(p);
+    }
+    sc = scratch_of[dev];
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaMemsetAsync(dev_tokens_per_expert, 0, sizeof(int32_t) * E, st));
+  if (T == 0) {
+    B200EP_CUDA(cudaMemsetAsync(dev_tokens_per_rank, 0, sizeof(int32_t) * world, st));
+    return B200EP_OK;
+  }
+  const int grid = (T + 255) / 256;
+  // the array still holds the previous call's ticket and totals: clear the part this call uses
+  B200EP_CUDA(cudaMemsetAsync(sc, 0, offsetof(LayoutStaticScratch, pub) + sizeof(unsigned long long) * kMaxRanks * grid, st));
+  const size_t smem = sizeof(int) * E;
+  const int el = E / world;
+  if (ids_i64)
+    layout_noalloc_kernel<int64_t><<<grid, 256, smem, st>>>((const int64_t*)dev_topk_ids, T, K, E, world, el,
+                                                          dev_tokens_per_rank, dev_tokens_per_expert,
+                                                          dev_is_token_in_rank, dev_send_off, sc);
+  else
+    layout_noalloc_kernel<int32_t><<<grid, 256, smem, st>>>((const int32_t*)dev_topk_ids, T, K, E, world, el,
+                                                          dev_tokens_per_rank, dev_tokens_per_expert,
+                                                          dev_is_token_in_rank, dev_send_off, sc);
+  B200EP_CUDA(cudaGetLastError());
+  return B200EP_OK;
+}
