@@ -1,0 +1,97 @@
+"""vLLM-facing classes that use b200ep's fused quantise+dispatch (SURVEY.md Route B).
+
+Route A (``llm-d_b200/deep_ep``) already lets vLLM's own DeepEP manager and prepare/finalize
+classes run on b200ep unchanged.  What Route A cannot do is skip the separate FP8 quantisation
+pass vLLM runs before the high-throughput dispatch
+(vllm/model_executor/layers/fused_moe/prepare_finalize/deepep_ht.py:282-289): the class below
+overrides just that step.  Everything else -- receiver, finalize, handles per DBO micro-batch,
+the manager (vllm/distributed/device_communicators/all2all.py:143-325) -- is inherited.
+
+``install()`` swaps the class in where vLLM constructs it
+(vllm/model_executor/layers/fused_moe/all2all_utils.py:155); call it from a
+``vllm.general_plugins`` entry point (vllm/plugins/__init__.py:14,69-82) so that every worker
+process does it.  The llm-d manifests keep ``--all2all-backend deepep_high_throughput``.
+"""
+from __future__ import annotations
+
+from typing import Callable
+
+import torch
+
+_classes = None
+
+
+def get_classes():
+    """Build the subclasses lazily (needs vLLM and the deep_ep shim importable)."""
+    global _classes
+    if _classes is not None:
+        return _classes
+
+    import deep_ep  # the b200ep shim (llm-d_b200/deep_ep)
+    import vllm.model_executor.layers.fused_moe.modular_kernel as mk
+    from vllm.model_executor.layers.fused_moe.config import FusedMoEQuantConfig
+    from vllm.model_executor.layers.fused_moe.prepare_finalize.deepep_ht import DeepEPHTPrepareAndFinalize
+    from vllm.v1.worker.ubatching import (dbo_current_ubatch_id, dbo_enabled, dbo_get_previous_event,
+                                          dbo_switch_to_compute_sync, dbo_yield_and_switch_from_compute_to_comm)
+
+    def _ue8m0_wanted() -> bool:
+        try:
+            from vllm.utils.deep_gemm import is_deep_gemm_e8m0_used
+
+            return bool(is_deep_gemm_e8m0_used())
+        except Exception:
+            return False
+
+    class B200EPHTPrepareAndFinalize(DeepEPHTPrepareAndFinalize):
+        """DeepEPHTPrepareAndFinalize with the FP8 block quantisation folded into the dispatch."""
+
+        @staticmethod
+        def can_fuse(buffer, a1: torch.Tensor, quant_config: FusedMoEQuantConfig, defer_input_quant: bool) -> bool:
+            bs = quant_config.block_shape
+            return (isinstance(buffer, deep_ep.Buffer) and hasattr(buffer, "_impl") and not defer_input_quant
+                    and quant_config.is_block_quantized and quant_config.quant_dtype == torch.float8_e4m3fn
+                    and bs is not None and bs[1] == 128 and not quant_config.per_act_token_quant
+                    and a1.dtype == torch.bfloat16 and a1.size(-1) % 128 == 0)
+
+        def prepare_async(self, a1: torch.Tensor, topk_weights: torch.Tensor, topk_ids: torch.Tensor, num_experts: int,
+                          expert_map: torch.Tensor | None, apply_router_weight_on_input: bool,
+                          quant_config: FusedMoEQuantConfig, defer_input_quant: bool = False) -> mk.ReceiverType:
+            if not self.can_fuse(self.buffer, a1, quant_config, defer_input_quant):
+                return super().prepare_async(a1, topk_weights, topk_ids, num_experts, expert_map,
+                                             apply_router_weight_on_input, quant_config, defer_input_quant)
+            if apply_router_weight_on_input:
+                assert topk_ids.size(1) == 1, "apply_router_weight_on_input is only implemented for topk=1"
+                a1 = a1 * topk_weights.to(a1.dtype)
+            return self._do_dispatch_fused(a1, topk_ids, topk_weights, num_experts, quant_config)
+
+        def _do_dispatch_fused(self, tokens, rank_topk_ids, rank_topk_weights, num_experts, quant_config) -> Callable:
+            # same sequence as DeepEPHTPrepareAndFinalize._do_dispatch (deepep_ht.py:97-181)
+            previous_event = dbo_get_previous_event(self.buffer.capture)
+            dbo_yield_and_switch_from_compute_to_comm()
+            (num_tokens_per_rank, num_tokens_per_rdma_rank, dispatch_expert_num_tokens, is_token_in_rank,
+             event) = self.buffer.get_dispatch_layout(topk_idx=rank_topk_ids, num_experts=num_experts,
+                                                      previous_event=previous_event, async_finish=False,
+                                                      allocate_on_comm_stream=False)
+            (token_data, expert_topk_ids, expert_topk_weights, expert_num_tokens_per_expert_list, handle,
+             event) = self.buffer.dispatch(
+                x=tokens, handle=None, num_tokens_per_rank=num_tokens_per_rank,
+                num_tokens_per_rdma_rank=num_tokens_per_rdma_rank, is_token_in_rank=is_token_in_rank,
+                num_tokens_per_expert=dispatch_expert_num_tokens, topk_idx=rank_topk_ids,
+                topk_weights=rank_topk_weights, expert_alignment=1, config=self._get_dispatch_config(),
+                previous_event=previous_event, async_finish=self.async_prepare and not dbo_enabled(),
+                allocate_on_comm_stream=False, b200ep_quantize=True, b200ep_ue8m0=_ue8m0_wanted())
+            self.handles[dbo_current_ubatch_id()] = handle
+            dbo_switch_to_compute_sync()
+            return lambda: self._receiver(event, True, token_data, expert_topk_ids, num_experts,
+                                          expert_num_tokens_per_expert_list, expert_topk_weights, None, quant_config,
+                                          defer_input_quant=False)
+
+    _classes = {"B200EPHTPrepareAndFinalize": B200EPHTPrepareAndFinalize}
+    return _classes
+
+
+def install() -> None:
+    """vLLM general-plugin hook: make maybe_make_prepare_finalize build the fused class."""
+    import vllm.model_executor.layers.fused_moe.all2all_utils as a2a
+
+    a2a.DeepEPHTPrepareAndFinalize = get_classes()["B200EPHTPrepareAndFinalize"]

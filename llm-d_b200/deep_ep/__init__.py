@@ -150,7 +150,12 @@ class Buffer:
     def dispatch(self, x, handle=None, num_tokens_per_rank=None, num_tokens_per_rdma_rank=None, is_token_in_rank=None,
                  num_tokens_per_expert=None, topk_idx=None, topk_weights=None, expert_alignment: int = 1,
                  num_worst_tokens: int = 0, config: Config | None = None, previous_event: EventOverlap | None = None,
-                 async_finish: bool = False, allocate_on_comm_stream: bool = False):
+                 async_finish: bool = False, allocate_on_comm_stream: bool = False, b200ep_quantize: bool = False,
+                 b200ep_ue8m0: bool = False):
+        """DeepEP signature plus two b200ep extensions: ``b200ep_quantize=True`` with a bf16 ``x``
+        quantises to e4m3 / 128-group fp32 scales INSIDE the dispatch kernel (what vLLM otherwise
+        does with per_token_group_quant_fp8 before the call, deepep_ht.py:282-289) and returns the
+        (recv_x, recv_scales) tuple; ``b200ep_ue8m0`` rounds those scales up to powers of two."""
         if handle is not None:
             raise NotImplementedError("b200ep: cached-handle re-dispatch is not used by vLLM and not provided")
         assert topk_idx is not None, "b200ep dispatch needs topk_idx"
@@ -165,11 +170,11 @@ class Buffer:
         with torch.cuda.stream(self._comm):
             rx, rs, ridx, rw, per_expert, h = self._impl.dispatch(
                 xq.contiguous(), topk_idx.contiguous(), None if topk_weights is None else topk_weights.contiguous(),
-                num_experts, x_scales=xs, layout=lay)
+                num_experts, x_scales=xs, layout=lay, quantize=b200ep_quantize, ue8m0=b200ep_ue8m0)
         ev = self._leave_comm(compute, async_finish, (xq, xs, topk_idx, topk_weights))
         if expert_alignment > 1:
             per_expert = [(n + expert_alignment - 1) // expert_alignment * expert_alignment for n in per_expert]
-        recv_x = (rx, rs) if xs is not None else rx
+        recv_x = (rx, rs) if rs is not None else rx
         return recv_x, ridx, rw, per_expert, h, ev
 
     def combine(self, x: torch.Tensor, handle, topk_weights=None, bias=None, config: Config | None = None,
