@@ -43,6 +43,7 @@ struct HtMeta {
   int32_t send_base[kMaxRanks];        // first row I own in rank d's receive region
   int32_t num_recv;
   int32_t pad[5];
+  int32_t send_count[kMaxRanks];       // tokens I send to rank d
   int32_t recv_per_expert[kMaxLocalExperts];
 };
 
@@ -53,6 +54,9 @@ struct Peers {
 // Region layout of one high-throughput slot (identical on every rank).
 struct HtPlan {
   size_t off_x, off_scales, off_idx, off_w, off_src, off_stage;
+  size_t off_qstage;    // local only: quantised rows [t_cap][qrow_bytes] staged before the ordered push
+  size_t off_sendlist;  // local only: int32 [world][t_cap], token sent to rank d at position p
+  int qrow_bytes;       // row_bytes + scale_bytes rounded up to 16
   int t_cap;       // tokens per rank the slot can take
   int cap_rows;    // world * t_cap receive rows
   int row_bytes;   // payload bytes per token (H for fp8, 2H for bf16)

@@ -24,6 +24,8 @@
 // Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> CTA barrier ->
 // fence.sys -> CTA counter -> (last CTA) st.release.sys flag in every peer;
 // consumers spin with ld.acquire.sys.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200ep {
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(256)
     int b = 0;
     for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * kMaxRanks + d]);
     meta->send_base[d] = b;
+    meta->send_count[d] = __ldcg(&cr[me * kMaxRanks + d]);
   }
   for (int i = tid; i < e_local; i += blockDim.x) {
     int n = 0;
@@ -228,6 +231,141 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kern
     }
   }
   if ((ttid >> 5) == 0) bulk_wait_all();
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
+}
+
+// ---- staged dispatch (W >= 3): quantise once, then push destination by destination.
+// With the direct kernel every rank fans each token out to a random subset of ranks; at W = 8
+// the fabric then behaves like an input-queued switch with head-of-line blocking (measured 54 %
+// of the peer-copy peak against 86 % for the permutation-ordered combine push).  The staged form
+// keeps the single quantisation pass but orders the NVLink traffic: rank r sends to r+1, r+2, ...
+// in interleaved rotation, so at any moment the ranks push along a permutation.
+
+// Phase 1: quantise (or copy) every token that leaves this rank into the local q-stage
+// [t][row | scales] and record send_list[d][p] = t.  Purely local: no flags, no system fence.
+template <int KIND>
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_stage_kernel(const __grid_constant__ HtDispatchArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
+  const int lane = tid & 31, twarp = ttid >> 5;
+  const int W = a.W, H = a.plan.H;
+  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes, qrow = a.plan.qrow_bytes;
+  const int stage_bytes = (qrow + 127) / 128 * 128;
+  char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
+  const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
+  const int nvec = in_row_bytes / 16;
+  char* my_slot = a.peers.base[a.me] + a.slot_off;
+  int32_t* send_list = reinterpret_cast<int32_t*>(my_slot + a.plan.off_sendlist);
+  int n = 0;
+
+  for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
+    int my_in = 0;
+    if (lane < W) my_in = a.in_rank[(size_t)t * W + lane];
+    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
+    if (dmask == 0) continue;  // uniform over the team
+    if (twarp == 1 && my_in) send_list[(size_t)lane * a.plan.t_cap + a.send_off[(size_t)t * W + lane]] = t;
+
+    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
+    int4 raw[kVpt];
+    load_pass(src, nvec, 0, ttid, raw);
+    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
+    float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+    ++n;
+    if (ttid == 0) {
+      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+    }
+    team_bar(team);
+    store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
+    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
+      load_pass(src, nvec, v0, ttid, raw);
+      store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
+    }
+    if (KIND == B200EP_X_FP8) {
+      const int ng = H / kGroup;
+      for (int g = ttid; g < ng; g += kTeamThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+    }
+    if (scale_bytes && ttid < (qrow - row_bytes - scale_bytes) / 4) s_scale[scale_bytes / 4 + ttid] = 0.f;  // pad
+    fence_proxy_async_smem();
+    team_bar(team);
+    if (ttid == 0) {
+      bulk_s2g(my_slot + a.plan.off_qstage + (size_t)t * qrow, s_row, qrow);
+      bulk_commit();
+    }
+  }
+  if (ttid == 0) bulk_wait_all();
+}
+
+// Phase 2: push.  Items interleave the W destinations starting at rank me+1 (self last).
+__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_push_kernel(const __grid_constant__ HtDispatchArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
+  const int lane = tid & 31, twarp = ttid >> 5;
+  const int W = a.W, K = a.plan.K;
+  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes, qrow = a.plan.qrow_bytes;
+  const int stage_bytes = (qrow + 127) / 128 * 128;
+  char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
+  const int nvec = qrow / 16;
+  const char* my_slot = a.peers.base[a.me] + a.slot_off;
+  const int32_t* send_list = reinterpret_cast<const int32_t*>(my_slot + a.plan.off_sendlist);
+  const char* qstage = my_slot + a.plan.off_qstage;
+  int n = 0;
+  int maxlen = 0;
+  for (int d = 0; d < W; ++d) maxlen = max(maxlen, a.meta->send_count[d]);
+  const long long items = (long long)maxlen * W;
+
+  for (long long i = (long long)blockIdx.x * kTeams + team; i < items; i += (long long)gridDim.x * kTeams) {
+    const int d = (a.me + 1 + (int)(i % W)) % W;
+    const int v = (int)(i / W);
+    if (v >= a.meta->send_count[d]) continue;  // uniform over the team
+    const int t = send_list[(size_t)d * a.plan.t_cap + v];
+    const int row = a.meta->send_base[d] + v;
+    const int4* src = reinterpret_cast<const int4*>(qstage + (size_t)t * qrow);
+    int4 raw[kVpt];
+#pragma unroll
+    for (int u = 0; u < kVpt; ++u) {
+      const int vv = u * kTeamThreads + ttid;
+      if (vv < nvec) raw[u] = ld_cg_v4(src + vv);  // written by the previous kernel: read through L2
+    }
+    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
+    ++n;
+    if (ttid == 0) {
+      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+    }
+    team_bar(team);
+#pragma unroll
+    for (int u = 0; u < kVpt; ++u) {
+      const int vv = u * kTeamThreads + ttid;
+      if (vv < nvec) reinterpret_cast<int4*>(s_row)[vv] = raw[u];
+    }
+    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
+      for (int vv = v0 + ttid; vv < min(nvec, v0 + kTeamThreads * kVpt); vv += kTeamThreads)
+        reinterpret_cast<int4*>(s_row)[vv] = ld_cg_v4(src + vv);
+    }
+    fence_proxy_async_smem();
+    team_bar(team);
+    char* dst = a.peers.base[d] + a.slot_off;
+    if (ttid == 0) {
+      bulk_s2g(dst + a.plan.off_x + (size_t)row * row_bytes, s_row, row_bytes);
+      if (scale_bytes && (scale_bytes & 15) == 0)
+        bulk_s2g(dst + a.plan.off_scales + (size_t)row * scale_bytes, s_row + row_bytes, scale_bytes);
+      bulk_commit();
+      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)row * 4) = t;
+    } else if (twarp == 1) {
+      if (lane < K) {
+        const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
+                                       : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
+        const float w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+        const bool mine = id >= 0 && (int)(id / a.e_local) == d;
+        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
+        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
+      }
+    } else if (twarp == 2 && scale_bytes && (scale_bytes & 15)) {
+      float* dsts = reinterpret_cast<float*>(dst + a.plan.off_scales + (size_t)row * scale_bytes);
+      const float* ss = reinterpret_cast<const float*>(s_row + row_bytes);
+      for (int g = lane; g < scale_bytes / 4; g += 32) dsts[g] = ss[g];
+    }
+  }
+  if (ttid == 0) bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
 }
 
@@ -497,19 +635,30 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.e_local = E / c->world;
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
-    const size_t stage_bytes = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    const size_t stage_bytes = (size_t)(plan.qrow_bytes + 127) / 128 * 128;
     a.nstage = 2 * kTeams * stage_bytes <= 100 * 1024 ? 2 : 1;  // two CTAs per SM must still fit
     const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
     const int grid = grid_for(c, T, kTeams, 2);
-    auto launch = [&](auto kern) -> int {
+    auto launch = [&](auto kern, int g) -> int {
       B200EP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      kern<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
+      kern<<<g, kTeams * kTeamThreads, smem, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
       return B200EP_OK;
     };
-    if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>);
-    else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>);
-    else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>);
+    // W >= 3: quantise once into the local q-stage, then push in permutation order (see above)
+    static const int staged_env = getenv("B200EP_HT_STAGED") ? atoi(getenv("B200EP_HT_STAGED")) : -1;
+    const bool staged = staged_env >= 0 ? (staged_env != 0 && c->world > 1) : c->world >= 3;
+    if (!staged) {
+      if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>, grid);
+      else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>, grid);
+      else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>, grid);
+    } else {
+      if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_stage_kernel<B200EP_X_BF16_QUANT>, grid);
+      else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_stage_kernel<B200EP_X_FP8>, grid);
+      else rc = launch(ht_dispatch_stage_kernel<B200EP_X_BF16>, grid);
+      if (rc) return rc;
+      rc = launch(ht_dispatch_push_kernel, grid_for(c, T * 6, kTeams, 2));
+    }
     if (rc) return rc;
   }
   if (phases & B200EP_PHASE_RECV) {
