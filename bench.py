@@ -60,62 +60,67 @@ def make_inputs(seed: int, tokens: int = T):
     return x.contiguous(), ids.to(torch.int64).contiguous(), w.contiguous()
 
 
+_SAMPLER_SRC = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[1]))
+period = float(sys.argv[2])
+print("max", nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM), flush=True)
+get_r = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+while True:
+    print(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), int(get_r(h)), flush=True)
+    time.sleep(period)
+"""
+
+
 class ClockSampler:
-    """SM clock and throttle reasons sampled DURING the timed region (profiling recipe), through NVML
-    in a background thread.  (A looping `nvidia-smi -lms` process was tried first: its queries stalled
-    rank 0's kernel launches by ~1 ms per step at N=4, so every other rank waited in the count exchange.)"""
+    """SM clock and throttle reasons of rank 0's GPU, sampled DURING the timed region by a helper
+    PROCESS that polls NVML (two light queries every 10 ms).
 
-    def __init__(self, index: int, period_s: float = 0.02):
-        self.index, self.period, self.samples, self.stop_flag, self.thread = index, period_s, [], False, None
-        self.mx = None
-        try:
-            import pynvml
+    Tried first and rejected because they slowed rank 0 down, and with it every rank that waits
+    for it in the count exchange: a looping `nvidia-smi -lms 100` (~1 ms per step at N=4), and
+    NVML polled from a thread of the benchmark process itself (initialising NVML in-process made
+    each kernel launch ~20 us slower: +150 us per step at N=2)."""
 
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
-        except Exception:
-            self.nv = None
-
-    def _one(self):
-        nv = self.nv
-        return (float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)),
-                int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons")
-                else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)))
-
-    def _run(self):
-        while not self.stop_flag:
-            try:
-                self.samples.append(self._one())
-            except Exception:
-                pass
-            time.sleep(self.period)
+    def __init__(self, index: int, period_s: float = 0.01):
+        self.index, self.period, self.lines, self.proc = index, period_s, [], None
 
     def start(self):
-        if self.nv is None:
-            return
-        self.samples.append(self._one())
-        self.thread = threading.Thread(target=self._run, daemon=True)
-        self.thread.start()
-
-    def stop(self):
-        if self.nv is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
-        self.stop_flag = True
-        self.thread.join(timeout=1.0)
         try:
-            self.samples.append(self._one())
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(self.index), str(self.period)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            first = self.proc.stdout.readline()  # wait until NVML is up, outside the timed region
+            self.mx = float(first.split()[1]) if first.startswith("max") else None
+            threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
-            pass
-        sm = sorted(s for s, _ in self.samples)
-        bits = 0
-        for _, r in self.samples:
-            bits |= r
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.perf_counter(), line))
+
+    def mark(self):
+        return time.perf_counter()
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml helper unavailable"]}
+        time.sleep(2.5 * self.period)
+        self.proc.terminate()
+        sm, bits = [], 0
+        for ts, ln in self.lines:
+            if t0 is not None and not (t0 <= ts <= t1 + 2 * self.period):
+                continue
+            p = ln.split()
+            if len(p) == 2:
+                sm.append(float(p[0])); bits |= int(p[1])
+        sm.sort()
         names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
                  0x80: "hw_power_brake_slowdown"}
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.mx,
-                "reasons": sorted(n for b, n in names.items() if bits & b), "samples": len(sm), "how": "NVML, 20 ms period"}
+                "reasons": sorted(n for b, n in names.items() if bits & b), "samples": len(sm),
+                "how": "NVML polled every 10 ms by a helper process while the timed steps ran"}
 
 
 def cpu_baseline(sample_tokens: int, repeats: int, threads: int | None = None):
@@ -262,14 +267,17 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    barrier()
     t_start, t_end = ev(), ev()
     t_start.record()
+    th0 = time.perf_counter()
     for i in range(steps):
         step(warm + i, True)
     t_end.record()
     torch.cuda.synchronize()
+    th1 = time.perf_counter()
     ms = t_start.elapsed_time(t_end)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(th0, th1) if rank == 0 else None
     tms = torch.tensor([ms], device=dev)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)

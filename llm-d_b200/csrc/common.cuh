@@ -22,12 +22,15 @@ constexpr int kNumSlots = B200EP_NUM_SLOTS;
 constexpr int kGroup = 128;  // FP8 quantisation group (DEEPEP_QUANT_BLOCK_SIZE, deepep_ll.py:28)
 
 // ---- symmetric control block (first kCtrlBytes of every rank's region; peers write it)
-enum FlagCat { kFlagHtNotify = 0, kFlagHtData, kFlagHtComb, kFlagLlCount, kFlagLlData, kFlagLlComb, kNumFlagCat };
+constexpr int kCombChunks = 8;     // the overlapped combine signals completion per chunk of source tokens
+constexpr int kCombChunkTokens = 512;
+enum FlagCat { kFlagHtNotify = 0, kFlagHtData, kFlagHtComb, kFlagLlCount, kFlagLlData, kFlagLlComb, kFlagHtCombChunk0,
+               kNumFlagCat = kFlagHtCombChunk0 + kCombChunks };
 constexpr size_t kFlagStride = 128;  // one flag per 128-byte line
 constexpr size_t kCtrlFlagsOff = 0;
 constexpr size_t kCtrlFlagsBytes = (size_t)kNumFlagCat * kNumSlots * kMaxRanks * kFlagStride;
-constexpr size_t kCtrlHtCntRankOff = 16384;  // int32 [slot][src][kMaxRanks]
-constexpr size_t kCtrlHtCntExpOff = 32768;   // int32 [slot][src][kMaxLocalExperts]
+constexpr size_t kCtrlHtCntRankOff = 65536;  // int32 [slot][src][kMaxRanks]
+constexpr size_t kCtrlHtCntExpOff = 81920;   // int32 [slot][src][kMaxLocalExperts]
 constexpr size_t kCtrlLlCntOff = kCtrlHtCntExpOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 4;
 constexpr size_t kCtrlBytes = 1 << 20;
 static_assert(kCtrlFlagsBytes <= kCtrlHtCntRankOff, "flags overflow");
@@ -280,7 +283,7 @@ void set_error(const char* fmt, ...);
 namespace b200ep {
 constexpr int kMaxLayoutBlocks = 1024;
 struct LocalScratch {
-  unsigned done[16];                                         // CTA-completion counters, one per kernel family
+  unsigned done[64];                                         // CTA-completion counters, one per kernel family
   unsigned long long layout_ticket;                          // monotonically increasing block ticket
   unsigned long long layout_pub[kMaxLayoutBlocks][kMaxRanks]; // (epoch << 32 | count) per block and rank
   HtMeta ht[kNumSlots];
