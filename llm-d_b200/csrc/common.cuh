@@ -290,12 +290,16 @@ struct LocalScratch {
   unsigned long long epoch[kNumFlagCat][kNumSlots];          // call epochs, advanced on the device
 };
 // pinned host mirror of the count exchange result
+// Every word is (low 32 bits of the call epoch << 32 | value): one 8-byte store is atomic over PCIe, so
+// the host can tell a fresh word from a stale one without the device issuing a system fence first.
+constexpr int kHostWordsPerSlot = 1 + (kMaxRanks + 1) + kMaxLocalExperts;  // num_recv, rank_prefix[], per_expert[]
 struct HostMirror {
-  volatile unsigned long long epoch[kNumSlots];
-  int32_t num_recv[kNumSlots];
-  int32_t rank_prefix[kNumSlots][kMaxRanks + 1];
-  int32_t recv_per_expert[kNumSlots][kMaxLocalExperts];
+  volatile unsigned long long word[kNumSlots][kHostWordsPerSlot];
+  int32_t num_recv_cache[kNumSlots];  // host-side copy made by b200ep_ht_notify_wait (sizes later grids)
 };
+__host__ __device__ inline unsigned long long host_word(unsigned long long epoch, int32_t v) {
+  return ((epoch & 0xffffffffull) << 32) | (unsigned long long)(uint32_t)v;
+}
 }  // namespace b200ep
 
 struct b200ep_ctx {

@@ -44,6 +44,41 @@ __global__ void __launch_bounds__(256)
   single_cta_signal(epoch_ptr, peers, W, kFlagHtNotify, slot, me);
 }
 
+// Derive this rank's receive offsets / totals from the count matrix and post them to the host.
+// counts come from the control block (filled by every rank's notify_send) or, for a single rank,
+// straight from the layout arrays (no exchange, no flags, no fence).
+__device__ __forceinline__ void notify_finish(const int32_t* cr, int cr_stride, const int32_t* ce, int ce_stride, int W,
+                                              int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
+                                              unsigned long long epoch) {
+  const int tid = threadIdx.x;
+  volatile unsigned long long* hw = host->word[slot];
+  if (tid == 0) {
+    int p = 0;
+    for (int s = 0; s < W; ++s) {
+      meta->rank_prefix[s] = p;
+      hw[1 + s] = host_word(epoch, p);
+      p += __ldcg(&cr[s * cr_stride + me]);
+    }
+    meta->rank_prefix[W] = p;
+    hw[1 + W] = host_word(epoch, p);
+    meta->num_recv = p;
+    hw[0] = host_word(epoch, p);
+  }
+  if (tid >= 32 && tid < 32 + W) {
+    const int d = tid - 32;
+    int b = 0;
+    for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * cr_stride + d]);
+    meta->send_base[d] = b;
+    meta->send_count[d] = __ldcg(&cr[me * cr_stride + d]);
+  }
+  for (int i = tid; i < e_local; i += blockDim.x) {
+    int n = 0;
+    for (int s = 0; s < W; ++s) n += __ldcg(&ce[(size_t)s * ce_stride + i]);
+    meta->recv_per_expert[i] = n;
+    hw[1 + kMaxRanks + 1 + i] = host_word(epoch, n);
+  }
+}
+
 __global__ void __launch_bounds__(256)
     ht_notify_recv_kernel(const char* my_base, int W, int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
                           const unsigned long long* epoch_ptr) {
@@ -51,37 +86,18 @@ __global__ void __launch_bounds__(256)
   const int32_t* cr = reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntRankOff) + (size_t)slot * kMaxRanks * kMaxRanks;
   const int32_t* ce =
       reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntExpOff) + (size_t)slot * kMaxRanks * kMaxLocalExperts;
-  const int tid = threadIdx.x;
-  if (tid == 0) {
-    int p = 0;
-    for (int s = 0; s < W; ++s) {
-      meta->rank_prefix[s] = p;
-      host->rank_prefix[slot][s] = p;
-      p += __ldcg(&cr[s * kMaxRanks + me]);
-    }
-    meta->rank_prefix[W] = p;
-    host->rank_prefix[slot][W] = p;
-    meta->num_recv = p;
-    host->num_recv[slot] = p;
-  }
-  if (tid >= 32 && tid < 32 + W) {
-    const int d = tid - 32;
-    int b = 0;
-    for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * kMaxRanks + d]);
-    meta->send_base[d] = b;
-    meta->send_count[d] = __ldcg(&cr[me * kMaxRanks + d]);
-  }
-  for (int i = tid; i < e_local; i += blockDim.x) {
-    int n = 0;
-    for (int s = 0; s < W; ++s) n += __ldcg(&ce[(size_t)s * kMaxLocalExperts + i]);
-    meta->recv_per_expert[i] = n;
-    host->recv_per_expert[slot][i] = n;
-  }
+  notify_finish(cr, kMaxRanks, ce, kMaxLocalExperts, W, me, slot, e_local, meta, host,
+                *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr));
+}
+
+// world == 1: the whole count "exchange" in one small kernel.
+__global__ void __launch_bounds__(256)
+    ht_notify_local_kernel(const int32_t* __restrict__ tok_per_rank, const int32_t* __restrict__ tok_per_expert, int slot,
+                           int e_local, HtMeta* meta, HostMirror* host, unsigned long long* epoch_ptr) {
+  const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
+  notify_finish(tok_per_rank, 1, tok_per_expert, e_local, 1, 0, slot, e_local, meta, host, epoch);
   __syncthreads();
-  if (tid == 0) {
-    __threadfence_system();
-    host->epoch[slot] = *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr);
-  }
+  if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
 }
 
 // ------------------------------------------------------------------ dispatch
@@ -231,7 +247,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kern
     }
   }
   if ((ttid >> 5) == 0) bulk_wait_all();
-  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
+  if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);  // a single rank has nobody to tell
 }
 
 // ---- staged dispatch (W >= 3): quantise once, then push destination by destination.
@@ -387,6 +403,7 @@ struct HtCombineArgs {
   size_t slot_off;
   unsigned long long* epoch_ptr;
   unsigned* chunk_done;  // [kCombChunks] private counters of the overlapped kernel
+  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished
   unsigned long long epoch_value;  // overlapped kernel only: the epoch this call publishes (host mirror; HT is never graph-captured)
   int T, W, me, slot, nstage;
 };
@@ -465,7 +482,7 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 // together (16 x 16 B per lane).  Accumulation order stays d = 0..W-1.
 constexpr int kRedVec = 4;
 __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
-  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
+  if (a.W > 1) cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H;
@@ -545,8 +562,11 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
   const int tid = threadIdx.x;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  const int role = blockIdx.x & 1, ridx = blockIdx.x >> 1;
-  const int nsend = (gridDim.x + 1) >> 1, nred = gridDim.x >> 1;
+  // three push CTAs for every reduce-only CTA (the NVLink transfer is what everything waits for);
+  // push CTAs join the reduction once their rows are out, reduce items are handed out dynamically
+  const int role = (blockIdx.x % 4 == 3) ? 1 : 0;
+  const int nred = gridDim.x / 4, nsend = gridDim.x - nred;
+  const int ridx = role ? blockIdx.x / 4 : blockIdx.x - blockIdx.x / 4;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
 
   if (role == 0) {
@@ -571,7 +591,24 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
       s_lo[k][c] = lo;
     }
     __syncthreads();
+    // Completion of chunk c is published one chunk late (after chunk c+1 has been issued), so the
+    // wait for the last rows of a chunk to land overlaps the next chunk's transfers.
+    auto arrive = [&](int c) {
+      __syncthreads();
+      if (tid == 0) {
+        const unsigned prev = atom_add_acq_rel_gpu(&a.chunk_done[c], 1u);
+        if (prev == (unsigned)nsend - 1) {
+          a.chunk_done[c] = 0;
+          fence_acq_rel_sys();
+          for (int d = 0; d < W; ++d)
+            if (d != a.me)
+              st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), a.epoch_value);
+          if (c == kCombChunks - 1) *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = a.epoch_value;
+        }
+      }
+    };
     for (int c = 0; c < kCombChunks; ++c) {
+      int issued = 0;  // bulk groups this team's issuing thread committed in chunk c
       int maxlen = 0;
       for (int k = 0; k < W - 1; ++k) maxlen = max(maxlen, s_lo[k][c + 1] - s_lo[k][c]);
       const long long items = (long long)maxlen * (W - 1);
@@ -600,25 +637,24 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
           const int t = __ldcg(src_idx + m);
           bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_row, row_bytes);
           bulk_commit();
+          ++issued;
         }
       }
-      // chunk c is drained on this CTA: arrive; the last push CTA publishes the chunk
-      if (ttid == 0) bulk_wait_all();
-      __syncthreads();
-      if (tid == 0) {
-        const unsigned prev = atom_add_acq_rel_gpu(&a.chunk_done[c], 1u);
-        if (prev == (unsigned)nsend - 1) {
-          a.chunk_done[c] = 0;
-          fence_acq_rel_sys();
-          for (int d = 0; d < W; ++d)
-            if (d != a.me)
-              st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), a.epoch_value);
-          if (c == kCombChunks - 1) *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = a.epoch_value;
+      if (c > 0) {
+        // everything older than this chunk's (>= 4) most recent groups has landed -> chunk c-1 is complete here
+        if (ttid == 0) {
+          if (issued >= 4) asm volatile("cp.async.bulk.wait_group 4;" ::: "memory");
+          else bulk_wait_all();
         }
+        arrive(c - 1);
       }
     }
-  } else {
-    // ------------------------------------------------ reduce role
+    if (ttid == 0) bulk_wait_all();
+    arrive(kCombChunks - 1);
+  }
+  {
+    // ------------------------------------------------ reduce (every CTA; push CTAs arrive late)
+    (void)nred;
     const int lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
     const int nsplit = nvec >= 256 ? 2 : 1;
     const int per = (nvec / nsplit + 31) / 32 * 32;
@@ -632,9 +668,13 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
                       a.epoch_value, kFlagHtCombChunk0 + c, a.me, tid);
       __syncthreads();
       if (t1 <= t0) continue;
-      const long long items = (long long)(t1 - t0) * nsplit;
-      for (long long it = (long long)ridx * nwarp + warp; it < items; it += (long long)nred * nwarp) {
-        const int t = t0 + (int)(it / nsplit), vbeg = (int)(it % nsplit) * per;
+      const int items = (t1 - t0) * nsplit;
+      for (;;) {
+        int it = 0;
+        if (lane == 0) it = (int)atomicAdd(&a.red_next[c], 1u);
+        it = __shfl_sync(0xffffffffu, it, 0);
+        if (it >= items) break;
+        const int t = t0 + it / nsplit, vbeg = (it % nsplit) * per;
         const int vend = min(nvec, vbeg + per);
         const char* rowp = nullptr;
         if (lane < W && a.in_rank[(size_t)t * W + lane]) {
@@ -686,6 +726,13 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
         }
       }
     }
+    // the last warp of the whole grid to run out of work rewinds the item counters for the next call
+    if (lane == 0) {
+      const unsigned prev = atomicAdd(&a.red_next[kCombChunks], 1u);
+      if (prev == gridDim.x * nwarp - 1) {
+        for (int c = 0; c <= kCombChunks; ++c) a.red_next[c] = 0;
+      }
+    }
   }
 }
 
@@ -725,6 +772,20 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
   cudaStream_t st = (cudaStream_t)stream;
   B200EP_CUDA(cudaSetDevice(c->device));
   const int el = E / c->world;
+  if (c->world == 1) {  // nothing to exchange: one kernel, issued with the first phase the caller asks for
+    if (phases & B200EP_PHASE_SEND) {
+      if (!dev_tokens_per_rank || !dev_tokens_per_expert) {
+        set_error("ht_notify: null counts");
+        return B200EP_ERR_ARG;
+      }
+      ++c->epoch[kFlagHtNotify][slot];
+      c->ht_e_local[slot] = el;
+      ht_notify_local_kernel<<<1, 256, 0, st>>>(dev_tokens_per_rank, dev_tokens_per_expert, slot, el, &c->local->ht[slot],
+                                               c->host_dev, &c->local->epoch[kFlagHtNotify][slot]);
+      B200EP_CUDA(cudaGetLastError());
+    }
+    return B200EP_OK;
+  }
   if (phases & B200EP_PHASE_SEND) {
     if (!dev_tokens_per_rank || !dev_tokens_per_expert) {
       set_error("ht_notify: null counts");
@@ -824,7 +885,7 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     }
     if (rc) return rc;
   }
-  if (phases & B200EP_PHASE_RECV) {
+  if ((phases & B200EP_PHASE_RECV) && c->world > 1) {  // a single rank has nobody to wait for
     wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, &c->local->epoch[kFlagHtData][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
@@ -882,6 +943,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.epoch_ptr = &c->local->epoch[kFlagHtComb][slot];
   const int row_bytes = 2 * H;
   a.chunk_done = &c->local->done[16 + slot * kCombChunks];
+  a.red_next = &c->local->done[32 + slot * 16];
   a.epoch_value = 0;
   static const int overlap_env = getenv("B200EP_HT_OVERLAP") ? atoi(getenv("B200EP_HT_OVERLAP")) : 1;
   if (phases == B200EP_PHASE_ALL && c->world > 1 && overlap_env) {
@@ -894,14 +956,13 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
     a.nstage = 2 * (size_t)kTeams * row_bytes <= 200 * 1024 ? 2 : 1;
     const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
     int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
-    grid &= ~1;
-    if (grid < 2) grid = 2;
+    if (grid < 4) grid = 4;
     B200EP_CUDA(cudaFuncSetAttribute(ht_combine_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ht_combine_fused_kernel<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
     return B200EP_OK;
   }
-  if (phases & B200EP_PHASE_SEND) {
+  if ((phases & B200EP_PHASE_SEND) && c->world > 1) {  // a single rank pushes nothing: the reduce reads dev_y directly
     ++c->epoch[kFlagHtComb][slot];  // host mirror of the device epoch (used by the overlapped path)
     a.nstage = 2 * (size_t)kTeams * row_bytes <= 100 * 1024 ? 2 : 1;
     int ctas_per_sm = 2;
@@ -910,7 +971,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
       ctas_per_sm = 1;
     }
     // M lives on the device; the host mirror of the last notify gives the grid size
-    const int M = c->host->num_recv[slot];
+    const int M = c->host->num_recv_cache[slot];
     const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
     B200EP_CUDA(cudaFuncSetAttribute(ht_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ht_combine_send_kernel<<<grid_for(c, M, kTeams, ctas_per_sm), kTeams * kTeamThreads, smem, st>>>(a);

@@ -39,36 +39,39 @@ struct LlScratch {  // private, per slot
 };
 static_assert(sizeof(LlScratch) * kNumSlots <= (4u << 20), "ll scratch");
 
+// Positions and counts from per-expert token bit masks: every (token, k) entry ORs its token's bit
+// into mask[e] (shared-memory atomics -- the resulting mask does not depend on arrival order), then
+// pos(t, e) = number of set bits below t and count[e] = popcount(mask[e]).  O(T*K) work, no scan loops.
 template <typename IdT>
 __global__ void __launch_bounds__(1024)
     ll_count_kernel(Peers peers, int W, int me, int slot, const IdT* __restrict__ ids, int T, int K, int E,
                     LlScratch* sc, unsigned long long* epoch_ptr) {
-  extern __shared__ int s_ids[];  // transposed [K][Tp] so that lanes read consecutive words
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-  const int Tp = (T + 31) / 32 * 32;
-  for (int i = tid; i < K * Tp; i += blockDim.x) {
-    const int k = i / Tp, t = i % Tp;
-    long long v = t < T ? (long long)ids[(size_t)t * K + k] : -1;
-    s_ids[i] = (v >= 0 && v < E) ? (int)v : -1;
+  extern __shared__ unsigned s_mask[];  // [E][nw]
+  const int tid = threadIdx.x;
+  const int nw = (T + 31) / 32;
+  for (int i = tid; i < E * nw; i += blockDim.x) s_mask[i] = 0u;
+  __syncthreads();
+  for (int i = tid; i < T * K; i += blockDim.x) {
+    const long long v = (long long)ids[i];
+    if (v >= 0 && v < E) atomicOr(&s_mask[(int)v * nw + (i / K) / 32], 1u << ((i / K) & 31));
   }
   __syncthreads();
-  for (int e = warp; e < E; e += nwarp) {
-    int base = 0;
-    for (int c = 0; c < Tp; c += 32) {
-      const int t = c + lane;
-      int hit = -1;
-      for (int k = 0; k < K; ++k)
-        if (s_ids[k * Tp + t] == e) hit = k;
-      const unsigned ball = __ballot_sync(0xffffffffu, hit >= 0);
-      if (hit >= 0) sc->pos[t * K + hit] = base + __popc(ball & ((1u << lane) - 1u));
-      base += __popc(ball);
+  for (int i = tid; i < T * K; i += blockDim.x) {
+    const long long v = (long long)ids[i];
+    if (v >= 0 && v < E) {
+      const int t = i / K;
+      const unsigned* m = &s_mask[(int)v * nw];
+      int p = __popc(m[t >> 5] & ((1u << (t & 31)) - 1u));
+      for (int w = 0; w < (t >> 5); ++w) p += __popc(m[w]);
+      sc->pos[i] = p;
     }
-    if (lane == 0) sc->cnt_mine[e] = base;
   }
-  __syncthreads();
-  for (int d = 0; d < W; ++d) {
-    int32_t* ce = reinterpret_cast<int32_t*>(peers.base[d] + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + me) * kLlMaxExperts;
-    for (int i = tid; i < E; i += blockDim.x) ce[i] = sc->cnt_mine[i];
+  for (int e = tid; e < E; e += blockDim.x) {
+    int n = 0;
+    for (int w = 0; w < nw; ++w) n += __popc(s_mask[e * nw + w]);
+    sc->cnt_mine[e] = n;
+    for (int d = 0; d < W; ++d)
+      (reinterpret_cast<int32_t*>(peers.base[d] + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + me) * kLlMaxExperts)[e] = n;
   }
   single_cta_signal(epoch_ptr, peers, W, kFlagLlCount, slot, me);
 }
@@ -345,14 +348,17 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
   if (phases & B200EP_LL_PHASE_COUNT) {
     c->ll_plan[slot] = plan;
     unsigned long long* ep = &c->local->epoch[kFlagLlCount][slot];
-    const int Tp = (T + 31) / 32 * 32;
-    const size_t smem = (size_t)K * Tp * 4;
+    const size_t smem = (size_t)E * ((T + 31) / 32) * 4;
+    if (smem > 160 * 1024) {
+      set_error("ll_dispatch: E=%d x T=%d needs %zu bytes of shared memory for the routing masks", E, T, smem);
+      return B200EP_ERR_ARG;
+    }
     if (ids_i64) {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
       ll_count_kernel<int64_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int64_t*)dev_topk_ids,
                                                      T, K, E, sc, ep);
     } else {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
       ll_count_kernel<int32_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int32_t*)dev_topk_ids,
                                                      T, K, E, sc, ep);
     }

@@ -272,9 +272,19 @@ int b200ep_ht_notify_wait(b200ep_ctx* c, int slot, int* num_recv_tokens, int32_t
     set_error("ht_notify_wait: bad slot");
     return B200EP_ERR_ARG;
   }
-  const uint64_t want = c->epoch[kFlagHtNotify][slot];
+  const uint64_t want = c->epoch[kFlagHtNotify][slot] & 0xffffffffull;
+  const int el = c->ht_e_local[slot];
+  volatile unsigned long long* hw = c->host->word[slot];
+  auto fresh = [&](int i) { return (hw[i] >> 32) == want; };
+  auto all_fresh = [&]() {
+    for (int i = 0; i <= c->world + 1; ++i)
+      if (!fresh(i)) return false;
+    for (int i = 0; i < el; ++i)
+      if (!fresh(1 + kMaxRanks + 1 + i)) return false;
+    return true;
+  };
   auto t0 = std::chrono::steady_clock::now();
-  while (c->host->epoch[slot] < want) {
+  while (!all_fresh()) {
     if (timeout_ms > 0 &&
         std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count() >
             timeout_ms) {
@@ -291,11 +301,12 @@ int b200ep_ht_notify_wait(b200ep_ctx* c, int slot, int* num_recv_tokens, int32_t
     std::this_thread::yield();
   }
   std::atomic_thread_fence(std::memory_order_acquire);
-  if (num_recv_tokens) *num_recv_tokens = c->host->num_recv[slot];
-  if (rank_prefix) memcpy(rank_prefix, (const void*)c->host->rank_prefix[slot], sizeof(int32_t) * (c->world + 1));
-  if (per_expert) {
-    memcpy(per_expert, (const void*)c->host->recv_per_expert[slot], sizeof(int32_t) * c->ht_e_local[slot]);
-  }
+  c->host->num_recv_cache[slot] = (int32_t)(uint32_t)hw[0];
+  if (num_recv_tokens) *num_recv_tokens = (int32_t)(uint32_t)hw[0];
+  if (rank_prefix)
+    for (int i = 0; i <= c->world; ++i) rank_prefix[i] = (int32_t)(uint32_t)hw[1 + i];
+  if (per_expert)
+    for (int i = 0; i < el; ++i) per_expert[i] = (int32_t)(uint32_t)hw[1 + kMaxRanks + 1 + i];
   return B200EP_OK;
 }
 
