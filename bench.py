@@ -239,25 +239,19 @@ def main():
     def step(i, timed):
         b = i % NBUF
         if args.breakdown and timed:
-            m = [ev() for _ in range(5)]
+            m = [ev() for _ in range(3)]
             th0 = time.perf_counter()
             m[0].record()
-        lay = buf.get_dispatch_layout(idss[b], E)
-        h, a = buf._dispatch_prepare(xs[b], idss[b], wss[b], E, None, True, False, lay)
-        buf.ht_notify(h.slot, lay)
+        # the public API: layout + count exchange (host wait) + fused quantise/dispatch in one call
+        rx, rs, ridx, rw, per_expert, h = buf.dispatch(xs[b], idss[b], wss[b], E, quantize=True)
         if args.breakdown and timed:
-            m[1].record(); th1 = time.perf_counter()
-        buf._dispatch_after_notify(h)
-        if args.breakdown and timed:
-            th2 = time.perf_counter(); m[2].record()
-        buf.ht_dispatch_launch(h, *a, L.PHASE_ALL)
-        if args.breakdown and timed:
-            m[3].record()
+            th1 = time.perf_counter()
+            m[1].record()
         y = y_pool[: h.num_recv]
         buf.combine(y, h, out)
         if args.breakdown and timed:
-            m[4].record(); marks.append((m, th1 - th0, th2 - th1))
-        last["h"], last["a"], last["y"] = h, a, y
+            m[2].record(); marks.append((m, th1 - th0, time.perf_counter() - th1))
+        last["h"], last["a"], last["y"] = h, (xs[b], None, idss[b], wss[b], False), y
         if timed:
             remote_copies.append(h.num_recv - (h.rank_prefix[rank + 1] - h.rank_prefix[rank]))
 
@@ -312,9 +306,9 @@ def main():
     del flush
     if args.breakdown:
         n = len(marks)
-        seg = [sum(m[j].elapsed_time(m[j + 1]) for m, _, _ in marks) / n * 1e3 for j in range(4)]
-        print(f"[rank {rank}] step breakdown us: layout+notify(gpu) {seg[0]:.1f} | host wait gap {seg[1]:.1f} | dispatch {seg[2]:.1f} "
-              f"| combine {seg[3]:.1f} || host launch {sum(a for _, a, _ in marks) / n * 1e6:.1f} host wait {sum(b for _, _, b in marks) / n * 1e6:.1f}",
+        seg = [sum(m[j].elapsed_time(m[j + 1]) for m, _, _ in marks) / n * 1e3 for j in range(2)]
+        print(f"[rank {rank}] step breakdown us: layout+notify+dispatch (gpu) {seg[0]:.1f} | combine (gpu) {seg[1]:.1f} || "
+              f"host in dispatch() {sum(a for _, a, _ in marks) / n * 1e6:.1f} host in combine() {sum(b for _, _, b in marks) / n * 1e6:.1f}",
               file=sys.stderr, flush=True)
     d_ms = sorted(p.elapsed_time(q) for p, q in k_disp)
     c_ms = sorted(p.elapsed_time(q) for p, q in k_comb)

@@ -166,6 +166,16 @@ int b200ep_ht_dispatch(b200ep_ctx* ctx, int slot, const void* dev_x, const float
                        const int32_t* dev_send_off, int T, int H, int K, int E, int phases,
                        void* stream);
 
+/* b200ep_layout + b200ep_ht_notify + b200ep_ht_notify_wait + b200ep_ht_dispatch (all phases) in one
+ * host call: the whole of deep_ep.Buffer.get_dispatch_layout + Buffer.dispatch (deepep_ht.py:121-162).
+ * The four layout arrays are outputs the caller keeps for the combine. */
+int b200ep_ht_dispatch_all(b200ep_ctx* ctx, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
+                           int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
+                           int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
+                           uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, int T, int H, int K, int E,
+                           int* num_recv_tokens, int32_t* per_expert, int32_t* rank_prefix, int timeout_ms,
+                           void* stream);
+
 typedef struct {
   void* recv_x;                /* [M, H] e4m3 or bf16 */
   float* recv_x_scales;        /* [M, H/128] fp32, NULL for B200EP_X_BF16 */

@@ -68,6 +68,8 @@ SIGNATURES = {
     "b200ep_ht_notify": (_i, [_p, _i, _p, _p, _i, _i, _p]),
     "b200ep_ht_notify_wait": (_i, [_p, _i, C.POINTER(_i), _p, _p, _i]),
     "b200ep_ht_dispatch": (_i, [_p, _i, _p, _p, _i, _i, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "b200ep_ht_dispatch_all": (_i, [_p, _i, _p, _p, _i, _i, _p, _i, _p, _p, _p, _p, _p, _i, _i, _i, _i, C.POINTER(_i), _p,
+                                    _p, _i, _p]),
     "b200ep_ht_views": (_i, [_p, _i, C.POINTER(HtView)]),
     "b200ep_ht_combine": (_i, [_p, _i, _p, _p, _p, _p, _i, _i, _i, _p]),
     "b200ep_ll_size_hint": (_sz, [_i, _i, _i, _i]),

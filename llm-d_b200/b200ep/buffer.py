@@ -239,11 +239,54 @@ class Buffer:
         quantised in the kernel when ``quantize``), or e4m3 [T,H] with ``x_scales``.
         Returns (recv_x, recv_x_scales, recv_topk_idx, recv_topk_weights,
         num_recv_tokens_per_expert_list, handle)."""
-        h, args = self._dispatch_prepare(x, topk_idx, topk_weights, num_experts, x_scales, quantize, ue8m0, layout)
-        self.ht_notify(h.slot, h.layout)
-        per_expert = self._dispatch_after_notify(h)
-        self.ht_dispatch_launch(h, *args, L.PHASE_ALL)
-        return (*self.ht_views(h)[:4], per_expert, h)
+        if layout is not None:
+            h, args = self._dispatch_prepare(x, topk_idx, topk_weights, num_experts, x_scales, quantize, ue8m0, layout)
+            self.ht_notify(h.slot, h.layout)
+            per_expert = self._dispatch_after_notify(h)
+            self.ht_dispatch_launch(h, *args, L.PHASE_ALL)
+            return (*self.ht_views(h)[:4], per_expert, h)
+        # no layout given: layout + count exchange + payload in ONE C call (b200ep_ht_dispatch_all)
+        T, H = x.shape
+        K = topk_idx.shape[1]
+        if x.dtype == torch.bfloat16:
+            kind = L.X_BF16_QUANT if quantize else L.X_BF16
+        elif x.dtype == torch.float8_e4m3fn:
+            kind = L.X_FP8
+            assert x_scales is not None and x_scales.dtype == torch.float32 and x_scales.is_contiguous()
+        else:
+            raise L.B200EPError(f"unsupported dispatch dtype {x.dtype}")
+        assert x.is_cuda and x.is_contiguous() and topk_idx.is_contiguous() and topk_idx.shape[0] == T
+        assert topk_weights is None or (topk_weights.dtype == torch.float32 and topk_weights.is_contiguous())
+        slot = self.next_slot()
+        lay = self._layout_tensors(slot, T, num_experts, x.device)
+        el = num_experts // self.world
+        n = C.c_int()
+        pe = (C.c_int32 * el)()
+        rp = (C.c_int32 * (self.world + 1))()
+        L.check(
+            self.lib.b200ep_ht_dispatch_all(
+                self.ctx, slot, _ptr(x), _ptr(x_scales), kind, int(ue8m0), _ptr(topk_idx),
+                int(topk_idx.dtype == torch.int64), _ptr(topk_weights), _ptr(lay.tokens_per_rank),
+                _ptr(lay.tokens_per_expert), _ptr(lay.is_token_in_rank), _ptr(lay.send_off), T, H, K, num_experts,
+                C.byref(n), pe, rp, 120000, _stream()),
+            "ht_dispatch_all",
+        )
+        h = HtHandle(slot, T, H, K, num_experts, kind, lay, n.value, list(rp), (x, x_scales, topk_idx, topk_weights))
+        return (*self.ht_views(h)[:4], list(pe), h)
+
+    def _layout_tensors(self, slot: int, T: int, E: int, dev) -> Layout:
+        """Layout outputs are needed until the matching combine; keep one set per slot and reuse it
+        while the shape stays the same (saves four allocator calls per dispatch)."""
+        cache = self.__dict__.setdefault("_lay_cache", {})
+        key = (slot, T, E, str(dev))
+        lay = cache.get(slot)
+        if lay is None or lay[0] != key:
+            lay = (key, Layout(torch.empty(self.world, dtype=torch.int32, device=dev),
+                               torch.empty(E, dtype=torch.int32, device=dev),
+                               torch.empty((T, self.world), dtype=torch.bool, device=dev),
+                               torch.empty((T, self.world), dtype=torch.int32, device=dev), E))
+            cache[slot] = lay
+        return lay[1]
 
     def _dispatch_prepare(self, x, topk_idx, topk_weights, num_experts, x_scales, quantize, ue8m0, layout):
         assert x.is_cuda and x.dim() == 2 and x.is_contiguous()

@@ -255,6 +255,51 @@ __device__ __forceinline__ uint2 quant8(const float (&f)[8], float s) {
   }
   return make_uint2(o[0], o[1]);
 }
+// ---- 32 bytes (16 bf16) per lane: one LDG.E.256 per lane, 8 lanes per 128-element group.  Halves the
+// per-group overhead (reciprocal, scale, shuffles) per element compared with 16-byte lanes.
+struct alignas(32) V8 {
+  uint32_t w[8];
+};
+__device__ __forceinline__ V8 ld_nc_v8(const void* p) {
+  V8 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]),
+                 "=r"(r.w[7])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ float group_amax8(float m) {
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+  return m;
+}
+// quantise the 16 bf16 values of `v` with the scale of their group -> 16 e4m3 bytes
+__device__ __forceinline__ float absmax16(const V8& v) {
+  float m = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    m = fmaxf(m, fabsf(__uint_as_float(v.w[i] << 16)));
+    m = fmaxf(m, fabsf(__uint_as_float(v.w[i] & 0xffff0000u)));
+  }
+  return m;
+}
+__device__ __forceinline__ uint4 quant16(const V8& v, float s) {
+  const float r = __frcp_rn(s);
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float f0 = __uint_as_float(v.w[2 * i] << 16), f1 = __uint_as_float(v.w[2 * i] & 0xffff0000u);
+    const float f2 = __uint_as_float(v.w[2 * i + 1] << 16), f3 = __uint_as_float(v.w[2 * i + 1] & 0xffff0000u);
+    const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(div_by_scale(f0, s, r), div_by_scale(f1, s, r)),
+                                                 __NV_SATFINITE, __NV_E4M3);
+    const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(div_by_scale(f2, s, r), div_by_scale(f3, s, r)),
+                                                 __NV_SATFINITE, __NV_E4M3);
+    o[i] = lo | (hi << 16);
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 // amax over the 16 lanes that hold one 128-element group
 __device__ __forceinline__ float group_amax16(float m) {
   m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
@@ -268,6 +313,9 @@ __device__ __forceinline__ float group_amax16(float m) {
 
 // ------------------------------------------------------------------ host side
 void set_error(const char* fmt, ...);
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) only when a kernel needs more than it already has:
+// the call costs several microseconds and the data kernels are launched every step.
+cudaError_t ensure_dynamic_smem(const void* kernel, int device, int bytes);
 #define B200EP_CUDA(call)                                                                        \
   do {                                                                                           \
     cudaError_t e_ = (call);                                                                     \

@@ -157,6 +157,33 @@ __device__ __forceinline__ void store_pass(const int4 (&raw)[kVpt], int nvec, in
   }
 }
 
+// Quantising passes with 32-byte lanes (KIND == B200EP_X_BF16_QUANT): 4 x 128 x 32 B = 16 KB per pass.
+constexpr int kVpt32 = 4;
+__device__ __forceinline__ void load_pass32(const V8* src, int nv32, int v0, int ttid, V8 (&raw)[kVpt32]) {
+#pragma unroll
+  for (int u = 0; u < kVpt32; ++u) {
+    const int v = v0 + u * kTeamThreads + ttid;
+    if (v < nv32) raw[u] = ld_nc_v8(src + v);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
+    }
+  }
+}
+__device__ __forceinline__ void quant_pass32(const V8 (&raw)[kVpt32], int nv32, int v0, int ttid, char* s_row,
+                                             float* s_scale, bool ue8m0) {
+#pragma unroll
+  for (int u = 0; u < kVpt32; ++u) {
+    const int v = v0 + u * kTeamThreads + ttid;
+    if (v0 + u * kTeamThreads >= nv32) break;  // uniform over the team
+    const float s = group_scale(group_amax8(absmax16(raw[u])), ue8m0);
+    if (v < nv32) {
+      reinterpret_cast<uint4*>(s_row)[v] = quant16(raw[u], s);
+      if ((ttid & 7) == 0) s_scale[v >> 3] = s;
+    }
+  }
+}
+
 // Persistent CTAs of four 128-thread teams.  Per row a team: issues every load of the row (up to
 // 16 KB in flight), waits until its previous TMA bulk copies have read the stage, quantises into
 // the stage, and warp 0 fans the row out with ONE cp.async.bulk per destination rank while warp 1
@@ -184,20 +211,36 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kern
     const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
     if (dmask == 0) continue;  // uniform over the team
 
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
-    int4 raw[kVpt];
-    load_pass(src, nvec, 0, ttid, raw);
     char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
     float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
     ++n;
-    if (twarp == 0) {  // the bulk copies that last used this stage have finished reading it
-      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
-    }
-    team_bar(team);
-    store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
-    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {  // rows wider than 16 KB
-      load_pass(src, nvec, v0, ttid, raw);
-      store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
+    if (KIND == B200EP_X_BF16_QUANT) {
+      const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
+      const int nv32 = nvec / 2;
+      V8 raw[kVpt32];
+      load_pass32(src, nv32, 0, ttid, raw);
+      if (twarp == 0) {  // the bulk copies that last used this stage have finished reading it
+        if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+      }
+      team_bar(team);
+      quant_pass32(raw, nv32, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
+      for (int v0 = kTeamThreads * kVpt32; v0 < nv32; v0 += kTeamThreads * kVpt32) {  // rows wider than 16 KB
+        load_pass32(src, nv32, v0, ttid, raw);
+        quant_pass32(raw, nv32, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
+      }
+    } else {
+      const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
+      int4 raw[kVpt];
+      load_pass(src, nvec, 0, ttid, raw);
+      if (twarp == 0) {
+        if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+      }
+      team_bar(team);
+      store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, false);
+      for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
+        load_pass(src, nvec, v0, ttid, raw);
+        store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, false);
+      }
     }
     if (KIND == B200EP_X_FP8) {
       const int ng = H / kGroup;
@@ -562,11 +605,12 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
   const int tid = threadIdx.x;
   const int W = a.W;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  // three push CTAs for every reduce-only CTA (the NVLink transfer is what everything waits for);
-  // push CTAs join the reduction once their rows are out, reduce items are handed out dynamically
-  const int role = (blockIdx.x % 4 == 3) ? 1 : 0;
-  const int nred = gridDim.x / 4, nsend = gridDim.x - nred;
-  const int ridx = role ? blockIdx.x / 4 : blockIdx.x - blockIdx.x / 4;
+  // CTAs alternate push / reduce-only; push CTAs join the reduction once their rows are out and
+  // reduce items are handed out dynamically.  (Measured at EP=8: 1:1 static 483 us, 3:1 502 us --
+  // with fewer reducers the reduction falls behind the transfer and becomes a tail.)
+  const int role = blockIdx.x & 1;
+  const int nred = gridDim.x >> 1, nsend = gridDim.x - nred;
+  const int ridx = blockIdx.x >> 1;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
 
   if (role == 0) {
@@ -862,7 +906,7 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
     const int grid = grid_for(c, T, kTeams, 2);
     auto launch = [&](auto kern, int g) -> int {
-      B200EP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      B200EP_CUDA(ensure_dynamic_smem((const void*)kern, c->device, (int)smem));
       kern<<<g, kTeams * kTeamThreads, smem, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
       return B200EP_OK;
@@ -957,7 +1001,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
     const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
     int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
     if (grid < 4) grid = 4;
-    B200EP_CUDA(cudaFuncSetAttribute(ht_combine_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_fused_kernel, c->device, (int)smem));
     ht_combine_fused_kernel<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
     return B200EP_OK;
@@ -973,7 +1017,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
     // M lives on the device; the host mirror of the last notify gives the grid size
     const int M = c->host->num_recv_cache[slot];
     const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
-    B200EP_CUDA(cudaFuncSetAttribute(ht_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_send_kernel, c->device, (int)smem));
     ht_combine_send_kernel<<<grid_for(c, M, kTeams, ctas_per_sm), kTeams * kTeamThreads, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
@@ -988,4 +1032,25 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
+}
+
+
+// One host call for the whole dispatch: layout -> count exchange -> host wait -> payload (+ wait).
+// Same kernels as the separate entry points; exists because at EP=1 the step is bound by the
+// caller's per-call overhead (ctypes crossings), not by the GPU.
+extern "C" int b200ep_ht_dispatch_all(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
+                                      int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
+                                      int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
+                                      uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, int T, int H, int K, int E,
+                                      int* num_recv_tokens, int32_t* per_expert, int32_t* rank_prefix, int timeout_ms,
+                                      void* stream) {
+  int rc = b200ep_layout(c, dev_topk_ids, ids_i64, T, K, E, dev_tokens_per_rank, dev_tokens_per_expert,
+                         dev_is_token_in_rank, dev_send_off, stream);
+  if (rc) return rc;
+  rc = b200ep_ht_notify(c, slot, dev_tokens_per_rank, dev_tokens_per_expert, E, B200EP_PHASE_ALL, stream);
+  if (rc) return rc;
+  rc = b200ep_ht_notify_wait(c, slot, num_recv_tokens, per_expert, rank_prefix, timeout_ms);
+  if (rc) return rc;
+  return b200ep_ht_dispatch(c, slot, dev_x, dev_x_scales, x_kind, ue8m0, dev_topk_ids, ids_i64, dev_topk_weights,
+                            dev_is_token_in_rank, dev_send_off, T, H, K, E, B200EP_PHASE_ALL, stream);
 }

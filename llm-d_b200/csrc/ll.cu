@@ -85,12 +85,21 @@ struct LlDispatchArgs {
   unsigned* done;
   size_t slot_off;
   unsigned long long *epoch_cnt_ptr, *epoch_data_ptr;
-  int T, W, me, slot, E, ue8m0, ids_i64;
+  int T, W, me, slot, E, ue8m0, ids_i64, fused, wait_data;
 };
 
+// fused == 1: the kernel also does the COUNT phase (production path, one launch for count + send):
+//   * the extra last CTA histograms this rank's ids, writes the counts to every peer and raises the
+//     count flags (its system fence overlaps the other CTAs' quantisation);
+//   * every token CTA computes the positions of its own token (how many earlier tokens of this rank
+//     chose the same expert) by itself, so it depends on nothing local.
+// wait_data == 1: the last CTA to finish also waits for every source's data flag, i.e. the kernel
+// completes when this rank's receive region is complete (no separate RECV launch).
 template <bool kFp8>
 __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_constant__ LlDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
+  __shared__ int s_pos[kMaxTopk];
+  __shared__ long long s_myid[kMaxTopk];
   const int tid = threadIdx.x, lane = tid & 31;
   const int W = a.W, K = a.plan.K, H = a.plan.H, e_local = a.plan.e_local, cap = a.plan.cap;
   const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
@@ -98,84 +107,152 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
   float* s_scale = reinterpret_cast<float*>(s_mem + row_bytes);
   const char* my_base = a.peers.base[a.me];
   const int32_t* cnt = reinterpret_cast<const int32_t*>(my_base + kCtrlLlCntOff) + (size_t)a.slot * kMaxRanks * kLlMaxExperts;
-  bool counts_ready = false;
+  auto load_id = [&](int t, int k) -> long long {
+    return a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + k]
+                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + k];
+  };
+  const int ntok_ctas = a.fused ? (int)gridDim.x - 1 : (int)gridDim.x;
 
-  for (int t = blockIdx.x; t < a.T || !counts_ready; t += gridDim.x) {
-    const bool have_token = t < a.T;
-    if (have_token) {
-      if (tid < K) bulk_wait_read0();  // issuing threads: previous copies have read the stage
-      __syncthreads();
-      const int4* src = reinterpret_cast<const int4*>(a.x + (size_t)t * H);
-      const int nvec = H / 8;
-      if (kFp8) {
-        for (int v0 = 0; v0 < nvec; v0 += 256) {
-          const int v = v0 + tid;
-          int4 raw = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
-          float f[8];
-          unpack8(raw, f);
-          float m = absmax8(f);
-          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
-          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-          m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-          const float s = group_scale(m, a.ue8m0 != 0);
-          if (v < nvec) {
-            *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
-            if ((lane & 15) == 0) s_scale[v >> 4] = s;
-          }
-        }
-      } else {
-        for (int v = tid; v < nvec; v += 256) reinterpret_cast<int4*>(s_row)[v] = ld_nc_v4(src + v);
-      }
-      fence_proxy_async_smem();
-    }
-    if (!counts_ready) {
-      cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt_ptr);
-      counts_ready = true;
-      if (blockIdx.x == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
-        for (int el = tid; el < e_local; el += blockDim.x) {
-          int p = 0;
-          for (int s = 0; s < W; ++s) {
-            const int n = __ldcg(&cnt[(size_t)s * kLlMaxExperts + a.me * e_local + el]);
-            a.sc->layout_range[(el * W + s) * 2] = p;
-            a.sc->layout_range[(el * W + s) * 2 + 1] = n;
-            p += n;
-          }
-          a.sc->recv_count[el] = p;
-        }
-      }
+  if (a.fused && (int)blockIdx.x == ntok_ctas) {
+    // ---------------- count role (one CTA): per-expert histogram -> every peer, count flags
+    int* s_cnt = reinterpret_cast<int*>(s_mem);
+    for (int e = tid; e < a.E; e += blockDim.x) s_cnt[e] = 0;
+    __syncthreads();
+    for (int i = tid; i < a.T * K; i += blockDim.x) {
+      const long long v = load_id(i / K, i % K);
+      if (v >= 0 && v < a.E) atomicAdd(&s_cnt[(int)v], 1);
     }
     __syncthreads();
-    if (have_token && tid < K) {
-      const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + tid]
-                                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + tid];
-      int slot_idx = -1;
-      if (id >= 0 && id < a.E) {
-        const int e = (int)id, d = e / e_local, el = e % e_local;
-        int base = 0;
-        for (int s = 0; s < a.me; ++s) base += __ldcg(&cnt[(size_t)s * kLlMaxExperts + e]);
-        slot_idx = base + a.sc->pos[t * K + tid];
-        if (slot_idx < cap) {
-          char* dst = a.peers.base[d] + a.slot_off;
-          const size_t r = (size_t)el * cap + slot_idx;
-          bulk_s2g(dst + a.plan.off_x + r * row_bytes, s_row, row_bytes);
-          if (kFp8 && (scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + r * scale_bytes, s_scale, scale_bytes);
-          bulk_commit();
-          if (kFp8 && (scale_bytes & 15)) {
-            float* ds = reinterpret_cast<float*>(dst + a.plan.off_scales + r * scale_bytes);
-            for (int g = 0; g < scale_bytes / 4; ++g) ds[g] = s_scale[g];
+    for (int e = tid; e < a.E; e += blockDim.x) {
+      const int n = s_cnt[e];
+      for (int d = 0; d < W; ++d)
+        (reinterpret_cast<int32_t*>(a.peers.base[d] + kCtrlLlCntOff) + ((size_t)a.slot * kMaxRanks + a.me) * kLlMaxExperts)[e] = n;
+    }
+    single_cta_signal(a.epoch_cnt_ptr, a.peers, W, kFlagLlCount, a.slot, a.me);
+  } else {
+    // count flags of this call carry (data epoch before this kernel) + 1: both advance once per dispatch,
+    // and the data epoch cannot move before every CTA of this kernel is past its waits
+    const unsigned long long want_cnt =
+        a.fused ? *reinterpret_cast<const volatile unsigned long long*>(a.epoch_data_ptr) + 1 : 0ull;
+    bool counts_ready = false;
+    for (int t = blockIdx.x; t < a.T || !counts_ready; t += ntok_ctas) {
+      const bool have_token = t < a.T;
+      if (have_token) {
+        if (tid < K) bulk_wait_read0();  // issuing threads: previous copies have read the stage
+        __syncthreads();
+        if (a.fused) {
+          if (tid < K) {
+            s_pos[tid] = 0;
+            s_myid[tid] = load_id(t, tid);
           }
-          *reinterpret_cast<int32_t*>(dst + a.plan.off_src + r * 4) = t * K + tid;
+          __syncthreads();
+          // how many earlier tokens of this rank chose each of my experts (== the COUNT kernel's pos)
+          for (int j0 = 0; j0 < t; j0 += blockDim.x) {
+            const int j = j0 + tid;
+            unsigned hit = 0;  // bit k: token j also routes to my k-th expert
+            if (j < t) {
+              for (int kk = 0; kk < K; ++kk) {
+                const long long v = load_id(j, kk);
+                if (v < 0) continue;
+                for (int k = 0; k < K; ++k)
+                  if (v == s_myid[k]) hit |= 1u << k;
+              }
+            }
+            for (int k = 0; k < K; ++k) {
+              const unsigned ball = __ballot_sync(0xffffffffu, (hit >> k) & 1u);
+              if (lane == 0 && ball) atomicAdd(&s_pos[k], __popc(ball));
+            }
+          }
+        }
+        const int4* src = reinterpret_cast<const int4*>(a.x + (size_t)t * H);
+        const int nvec = H / 8;
+        if (kFp8) {
+          for (int v0 = 0; v0 < nvec; v0 += 256) {
+            const int v = v0 + tid;
+            int4 raw = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
+            float f[8];
+            unpack8(raw, f);
+            const float s = group_scale(group_amax16(absmax8(f)), a.ue8m0 != 0);
+            if (v < nvec) {
+              *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
+              if ((lane & 15) == 0) s_scale[v >> 4] = s;
+            }
+          }
         } else {
-          printf("b200ep: rank %d ll_dispatch overflow: expert %d slot %d >= capacity %d\n", a.me, e, slot_idx, cap);
-          __trap();
+          for (int v = tid; v < nvec; v += 256) reinterpret_cast<int4*>(s_row)[v] = ld_nc_v4(src + v);
+        }
+        fence_proxy_async_smem();
+      }
+      if (!counts_ready) {
+        if (a.fused) {
+          if (tid < W)
+            wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(kFlagLlCount, a.slot, tid)), want_cnt,
+                          kFlagLlCount, a.me, tid);
+          __syncthreads();
+        } else {
+          cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt_ptr);
+        }
+        counts_ready = true;
+        if (blockIdx.x == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
+          for (int el = tid; el < e_local; el += blockDim.x) {
+            int p = 0;
+            for (int s = 0; s < W; ++s) {
+              const int n = __ldcg(&cnt[(size_t)s * kLlMaxExperts + a.me * e_local + el]);
+              a.sc->layout_range[(el * W + s) * 2] = p;
+              a.sc->layout_range[(el * W + s) * 2 + 1] = n;
+              p += n;
+            }
+            a.sc->recv_count[el] = p;
+          }
         }
       }
-      a.sc->send_slot[t * K + tid] = slot_idx;
+      __syncthreads();
+      if (have_token && tid < K) {
+        const long long id = load_id(t, tid);
+        int slot_idx = -1;
+        if (id >= 0 && id < a.E) {
+          const int e = (int)id, d = e / e_local, el = e % e_local;
+          int base = 0;
+          for (int s = 0; s < a.me; ++s) base += __ldcg(&cnt[(size_t)s * kLlMaxExperts + e]);
+          slot_idx = base + (a.fused ? s_pos[tid] : a.sc->pos[t * K + tid]);
+          if (slot_idx < cap) {
+            char* dst = a.peers.base[d] + a.slot_off;
+            const size_t r = (size_t)el * cap + slot_idx;
+            bulk_s2g(dst + a.plan.off_x + r * row_bytes, s_row, row_bytes);
+            if (kFp8 && (scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + r * scale_bytes, s_scale, scale_bytes);
+            bulk_commit();
+            if (kFp8 && (scale_bytes & 15)) {
+              float* ds = reinterpret_cast<float*>(dst + a.plan.off_scales + r * scale_bytes);
+              for (int g = 0; g < scale_bytes / 4; ++g) ds[g] = s_scale[g];
+            }
+            *reinterpret_cast<int32_t*>(dst + a.plan.off_src + r * 4) = t * K + tid;
+          } else {
+            printf("b200ep: rank %d ll_dispatch overflow: expert %d slot %d >= capacity %d\n", a.me, e, slot_idx, cap);
+            __trap();
+          }
+        }
+        a.sc->send_slot[t * K + tid] = slot_idx;
+      }
+    }
+    if (tid < K) bulk_wait_all();
+  }
+  // every CTA (count role included): completion counter, last one raises the data flags
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned prev = atom_add_acq_rel_gpu(a.done, 1u);
+    if (prev == gridDim.x - 1) {
+      *a.done = 0;
+      const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(a.epoch_data_ptr) + 1;
+      fence_acq_rel_sys();
+      for (int d = 0; d < W; ++d)
+        st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagLlData, a.slot, a.me)), epoch);
+      *reinterpret_cast<volatile unsigned long long*>(a.epoch_data_ptr) = epoch;
+      if (a.wait_data)
+        for (int s = 0; s < W; ++s)
+          wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(kFlagLlData, a.slot, s)), epoch, kFlagLlData,
+                        a.me, s);
     }
   }
-  if (tid < K) bulk_wait_all();
-  cta_done_then_signal(a.done, a.epoch_data_ptr, a.peers, W, kFlagLlData, a.slot, a.me);
 }
 
 struct LlCombineArgs {
@@ -189,11 +266,17 @@ struct LlCombineArgs {
   unsigned* done;
   size_t slot_off;
   unsigned long long* epoch_ptr;
-  int T, W, me, slot, E, ids_i64;
+  int T, W, me, slot, E, ids_i64, fused;
 };
 
+__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a);
+
+// a.fused == 1 (all phases in one call): after its pushes every CTA waits for the peers' flags and
+// takes part in the reduction, so the whole combine is one launch.
 __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_constant__ LlCombineArgs a) {
   extern __shared__ __align__(128) char s_mem[];
+  // the epoch this call publishes; read before any CTA can have advanced it (that needs all CTAs to arrive)
+  const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(a.epoch_ptr) + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W, K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
@@ -234,12 +317,18 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
   }
   bulk_wait_all();
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagLlComb, a.slot, a.me);
+  if (a.fused) {
+    if ((int)threadIdx.x < W)
+      wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagLlComb, a.slot, threadIdx.x)), want,
+                    kFlagLlComb, a.me, threadIdx.x);
+    __syncthreads();
+    ll_reduce_items(a);
+  }
 }
 
 // out[t] = bf16( sum_k w[t,k] * row(t,k) ): fp32 multiply, fp32 add, k ascending.
 // A warp owns (token, 512-byte column block) so that 128 tokens still fill the GPU.
-__global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_constant__ LlCombineArgs a) {
-  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch_ptr);
+__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
@@ -298,6 +387,11 @@ __global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_const
   }
 }
 
+__global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_constant__ LlCombineArgs a) {
+  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch_ptr);
+  ll_reduce_items(a);
+}
+
 __global__ void ll_wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
                                        const unsigned long long* epoch_ptr) {
   cta_wait_all_sources(my_base, W, cat, slot, me, epoch_ptr);
@@ -345,8 +439,11 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
     return B200EP_ERR_ARG;
   }
   LlScratch* sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
-  if (phases & B200EP_LL_PHASE_COUNT) {
-    c->ll_plan[slot] = plan;
+  // COUNT and SEND requested together (the normal case): one launch does both.  Phase-by-phase callers
+  // (single-GPU emulation of several ranks) get the separate count kernel.
+  const bool fused = (phases & B200EP_LL_PHASE_COUNT) && (phases & B200EP_LL_PHASE_SEND);
+  if (phases & B200EP_LL_PHASE_COUNT) c->ll_plan[slot] = plan;
+  if ((phases & B200EP_LL_PHASE_COUNT) && !fused) {
     unsigned long long* ep = &c->local->epoch[kFlagLlCount][slot];
     const size_t smem = (size_t)E * ((T + 31) / 32) * 4;
     if (smem > 160 * 1024) {
@@ -354,16 +451,17 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
       return B200EP_ERR_ARG;
     }
     if (ids_i64) {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ll_count_kernel<int64_t>, c->device, 160 * 1024));
       ll_count_kernel<int64_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int64_t*)dev_topk_ids,
                                                      T, K, E, sc, ep);
     } else {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_count_kernel<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ll_count_kernel<int32_t>, c->device, 160 * 1024));
       ll_count_kernel<int32_t><<<1, 1024, smem, st>>>(c->peers, c->world, c->rank, slot, (const int32_t*)dev_topk_ids,
                                                      T, K, E, sc, ep);
     }
     B200EP_CUDA(cudaGetLastError());
   }
+  const bool wait_in_kernel = fused && (phases & B200EP_LL_PHASE_RECV);
   if (phases & B200EP_LL_PHASE_SEND) {
     LlDispatchArgs a;
     a.peers = c->peers;
@@ -382,18 +480,21 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
     a.E = E;
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
-    const size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
-    const int grid = ll_grid(c, T);
+    a.fused = fused ? 1 : 0;
+    a.wait_data = wait_in_kernel ? 1 : 0;
+    size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
+    if (fused && smem < (size_t)E * 4) smem = (size_t)E * 4;  // the count CTA's histogram
+    const int grid = ll_grid(c, T) + (fused ? 1 : 0);
     if (use_fp8) {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_dispatch_send_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ll_dispatch_send_kernel<true>, c->device, (int)smem));
       ll_dispatch_send_kernel<true><<<grid, 256, smem, st>>>(a);
     } else {
-      B200EP_CUDA(cudaFuncSetAttribute(ll_dispatch_send_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ll_dispatch_send_kernel<false>, c->device, (int)smem));
       ll_dispatch_send_kernel<false><<<grid, 256, smem, st>>>(a);
     }
     B200EP_CUDA(cudaGetLastError());
   }
-  if (phases & B200EP_LL_PHASE_RECV) {
+  if ((phases & B200EP_LL_PHASE_RECV) && !wait_in_kernel) {
     ll_wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagLlData, slot, c->rank, &c->local->epoch[kFlagLlData][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
@@ -449,6 +550,7 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
   a.E = E;
   a.ids_i64 = ids_i64;
   a.epoch_ptr = &c->local->epoch[kFlagLlComb][slot];
+  a.fused = (phases == B200EP_PHASE_ALL) ? 1 : 0;
   const int row_bytes = 2 * H;
   if (phases & B200EP_PHASE_SEND) {
     if (!dev_y) {
@@ -460,11 +562,11 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
     if (warps < 1) warps = 1;
     const size_t smem = (size_t)warps * row_bytes;
     const int grid = ll_grid(c, c->num_sms);
-    B200EP_CUDA(cudaFuncSetAttribute(ll_combine_send_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200EP_CUDA(ensure_dynamic_smem((const void*)ll_combine_send_kernel, c->device, (int)smem));
     ll_combine_send_kernel<<<grid, warps * 32, smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
-  if (phases & B200EP_PHASE_RECV) {
+  if ((phases & B200EP_PHASE_RECV) && !a.fused) {
     if (T > 0 && (!dev_out || !dev_topk_ids || !dev_topk_weights)) {
       set_error("ll_combine: null pointer");
       return B200EP_ERR_ARG;

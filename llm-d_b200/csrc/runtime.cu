@@ -9,6 +9,8 @@
 #include <string.h>
 
 #include <atomic>
+#include <map>
+#include <mutex>
 #include <chrono>
 #include <new>
 #include <thread>
@@ -27,6 +29,17 @@ void set_error(const char* fmt, ...) {
 }
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+cudaError_t ensure_dynamic_smem(const void* kernel, int device, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> have;
+  std::lock_guard<std::mutex> lock(mu);
+  int& cur = have[{kernel, device}];
+  if (bytes <= cur) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) cur = bytes;
+  return e;
+}
 
 // One slot of the high-throughput mode:
 //   receive side  (written by peers' dispatch): x rows, scales, top-k ids, top-k weights, source index

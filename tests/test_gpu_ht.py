@@ -134,3 +134,25 @@ def test_ht_capacity_error_is_loud():
             world.bufs[0].dispatch(x.to(DEV), ids.to(DEV), w.to(DEV), 256, quantize=True)
     finally:
         world.destroy()
+
+
+def test_ht_one_call_dispatch_single_rank():
+    """Buffer.dispatch without a precomputed layout goes through b200ep_ht_dispatch_all (one host call)."""
+    from b200ep import Buffer
+
+    T, H, E, K = 300, 1024, 32, 8
+    buf = Buffer(None, sym_bytes=128 << 20, rank=0, world=1)
+    try:
+        for it in range(3):
+            x, ids, w = make_rank_inputs(T + it, H, E, K, seed=90 + it, mask_frac=0.15)
+            q, s = fp8.group_quant_fp8(bf16_bits(x))
+            ref = dispatch.ht_dispatch([q], [ids.numpy()], [w.numpy()], E, scales=[s])
+            rx, rs, ridx, rw, per_expert, h = buf.dispatch(x.to(DEV), ids.to(DEV), w.to(DEV), E, quantize=True)
+            rsrc = buf.ht_views(h)[4]
+            _check_dispatch([(rx, rs, ridx, rw, rsrc, per_expert, h)], ref, "quant", K)
+            y = bits.f32_to_bf16(fp8.dequant_fp8(ref[0]["recv_x"], ref[0]["recv_x_scales"]))
+            out = buf.combine(bits_to_bf16(y, DEV), h)
+            want = combine.ht_combine([y], ref, [T + it])[0]
+            assert np.array_equal(bf16_bits(out), want)
+    finally:
+        buf.destroy()

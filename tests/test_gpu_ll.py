@@ -80,3 +80,40 @@ def test_ll_decode_shape_roundtrip():
         assert (out.float() - ref).abs().max().item() <= 0.08 * ref.abs().max().item()
     finally:
         world.destroy()
+
+
+@pytest.mark.parametrize("hook", [False, True])
+def test_ll_single_launch_paths_single_rank(hook):
+    """The production entry points (count+send in one launch, optional recv hook, one-launch combine)
+    on one rank, against the oracle -- the phase-by-phase kernels are covered above."""
+    from b200ep import Buffer
+
+    T, H, E, K, max_tok = 57, 2048, 32, 8, 64
+    buf = Buffer(None, sym_bytes=256 << 20, rank=0, world=1)
+    try:
+        for it in range(3):  # repeated calls: epochs and both slots
+            x, ids, w = make_rank_inputs(T - it, H, E, K, seed=40 + it, mask_frac=0.1 * it)
+            q, s = fp8.group_quant_fp8(bf16_bits(x))
+            ref = dispatch.ll_dispatch([q], [ids.numpy()], E, max_tok, scales=[s])[0]
+            px, ps, cnt, h, hk = buf.low_latency_dispatch(x.to(DEV), ids.to(DEV), max_tok, E, use_fp8=True,
+                                                          return_recv_hook=hook)
+            if hook:
+                hk()
+            torch.cuda.synchronize()
+            assert np.array_equal(cnt.cpu().numpy(), ref["recv_count"])
+            y = np.zeros((E, max_tok, H), np.float32)
+            for el in range(E):
+                n = int(ref["recv_count"][el])
+                assert np.array_equal(u8(px)[el, :n], ref["packed_recv_x"][el, :n])
+                assert np.array_equal(ps.cpu().numpy()[el, :n], ref["packed_recv_scales"][el, :n])
+                assert np.array_equal(h.src_info.cpu().numpy()[el, :n], ref["src_info"][el, :n])
+                y[el, :n] = fp8.dequant_fp8(ref["packed_recv_x"][el, :n], ref["packed_recv_scales"][el, :n]) * (1 + el)
+            yb = bits.f32_to_bf16(y.reshape(-1, H)).reshape(E, max_tok, H)
+            out, chk = buf.low_latency_combine(bits_to_bf16(yb, DEV), ids.to(DEV), w.to(DEV), h, return_recv_hook=hook)
+            if hook:
+                chk()
+            torch.cuda.synchronize()
+            want = combine.ll_combine([yb], [ids.numpy()], [w.numpy()], [ref], E)[0]
+            assert np.array_equal(bf16_bits(out), want)
+    finally:
+        buf.destroy()
