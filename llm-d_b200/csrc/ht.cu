@@ -293,6 +293,97 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kern
   if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);  // a single rank has nobody to tell
 }
 
+// ---- warp-granular quantising dispatch (KIND == B200EP_X_BF16_QUANT, rows up to 8192 elements).
+// ncu on the team kernel at EP=1: 21 % of the stall samples were team barriers and 24 % first uses of
+// loaded data, issue slots 56 % busy.  Here every warp owns whole rows and a private shared-memory
+// stage, so nothing but __syncwarp separates load -> quantise -> TMA fan-out, and 24 independent
+// warps per SM (one 768-thread CTA, <= 85 registers) keep 4 x 32 B x 32 lanes each in flight.
+constexpr int kWarpCtaWarps = 24;
+__global__ void __launch_bounds__(kWarpCtaWarps * 32, 1) ht_dispatch_send_warp_kernel(const __grid_constant__ HtDispatchArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int W = a.W, K = a.plan.K, H = a.plan.H;
+  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
+  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
+  char* s_row = s_mem + (size_t)warp * stage_bytes;
+  float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+  const int nv32 = H / 16;
+  const bool ue8m0 = a.ue8m0 != 0;
+
+  for (int t = blockIdx.x * kWarpCtaWarps + warp; t < a.T; t += gridDim.x * kWarpCtaWarps) {
+    int my_in = 0, my_row = -1;
+    if (lane < W) {
+      my_in = a.in_rank[(size_t)t * W + lane];
+      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
+    }
+    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
+    if (dmask == 0) continue;
+    const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
+    bool stage_free = false;
+    for (int v0 = 0; v0 < nv32; v0 += 32 * kVpt32) {
+      V8 raw[kVpt32];
+#pragma unroll
+      for (int u = 0; u < kVpt32; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v < nv32) raw[u] = ld_nc_v8(src + v);
+        else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
+        }
+      }
+      if (!stage_free) {  // loads are in flight; now make sure the previous row's copies have read the stage
+        bulk_wait_read0();
+        __syncwarp();
+        stage_free = true;
+      }
+#pragma unroll
+      for (int u = 0; u < kVpt32; ++u) {
+        const int v = v0 + u * 32 + lane;
+        if (v0 + u * 32 >= nv32) break;  // uniform over the warp
+        const float s = group_scale(group_amax8(absmax16(raw[u])), ue8m0);
+        if (v < nv32) {
+          reinterpret_cast<uint4*>(s_row)[v] = quant16(raw[u], s);
+          if ((lane & 7) == 0) s_scale[v >> 3] = s;
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (my_in) {
+      char* dst = a.peers.base[lane] + a.slot_off;
+      bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
+      if ((scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
+      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+    }
+    bulk_commit();
+    // metadata: top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
+    long long id = -1;
+    float w = 0.f;
+    if (lane < K) {
+      id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
+                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
+      w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+    }
+    const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
+    for (int d = 0; d < W; ++d) {
+      if (!((dmask >> d) & 1u)) continue;
+      const int row = __shfl_sync(0xffffffffu, my_row, d);
+      char* dst = a.peers.base[d] + a.slot_off;
+      if (lane < K) {
+        const bool mine = owner == d;
+        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
+        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
+      }
+      if (scale_bytes & 15) {  // scale vector not a 16-byte multiple: plain stores
+        float* dsts = reinterpret_cast<float*>(dst + a.plan.off_scales + (size_t)row * scale_bytes);
+        for (int g = lane; g < scale_bytes / 4; g += 32) dsts[g] = s_scale[g];
+      }
+    }
+  }
+  bulk_wait_all();
+  if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
+}
+
 // ---- staged dispatch (W >= 3): quantise once, then push destination by destination.
 // With the direct kernel every rank fans each token out to a random subset of ranks; at W = 8
 // the fabric then behaves like an input-queued switch with head-of-line blocking (measured 54 %
@@ -916,7 +1007,15 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     // the direct kernel stays the default; the staged form is kept for experiments.
     static const int staged_env = getenv("B200EP_HT_STAGED") ? atoi(getenv("B200EP_HT_STAGED")) : 0;
     const bool staged = staged_env != 0 && c->world > 1;
-    if (!staged) {
+    // Experiment, off by default: measured 31.0 us at EP=1 against 26.5 us for the team kernel (fewer
+    // instructions, 9.8 M vs 11.9 M, but each warp serialises load -> quantise over 3.5 passes per row).
+    static const int warp_env = getenv("B200EP_HT_WARP_KERNEL") ? atoi(getenv("B200EP_HT_WARP_KERNEL")) : 0;
+    if (!staged && x_kind == B200EP_X_BF16_QUANT && warp_env && kWarpCtaWarps * stage_bytes <= 220 * 1024) {
+      const size_t wsmem = (size_t)kWarpCtaWarps * stage_bytes;
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ht_dispatch_send_warp_kernel, c->device, (int)wsmem));
+      ht_dispatch_send_warp_kernel<<<grid_for(c, T, kWarpCtaWarps, 1), kWarpCtaWarps * 32, wsmem, st>>>(a);
+      B200EP_CUDA(cudaGetLastError());
+    } else if (!staged) {
       if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>, grid);
       else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>, grid);
       else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>, grid);
