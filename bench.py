@@ -401,7 +401,11 @@ def main():
         dominant = "ht_combine_recv_kernel (fp32 reduce)" if c_k >= d_k else "ht_dispatch_send_kernel (fused quantise)"
     dom_gbs = c_gbs if c_k >= d_k else d_gbs
     roofline = {
-        "bound": bound, "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak, "traffic": None,
+        "bound": bound, "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
+        # dram__bytes_read+write per launch from the ncu --set full capture of round 1 (profiles/r01_ncu_full_n1.txt),
+        # N=1 only: reduce kernel 58.8 MB read + 9.9 MB written (the rest of the 58.7 MB output is still in L2),
+        # dispatch kernel 59.2 + 4.2 MB
+        "traffic": (None if world > 1 else (68.68e6 if c_k >= d_k else 63.40e6)),
         "kernel": dominant, "peak_source": unit_note,
         "how": "CUDA events around each kernel, launches queued back to back, L2 flushed (512 MB read) before each; "
                "N>1: push kernels only (max over ranks), N=1: dispatch send kernel and reduce kernel",
@@ -475,7 +479,7 @@ def main():
                        "l2": f"{NBUF} rotating input sets ({NBUF * (T * H * 2) >> 20} MiB of x) > 126 MB L2",
                        "tokens_per_s_per_gpu": value / world},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
-            "gpu_launches": steps * 7 + R * 4, "ll": ll,
+            "gpu_launches": steps * (4 if world == 1 else 6) + R * (2 if world == 1 else 4), "ll": ll,
         }
         print(json.dumps(line))
     buf.destroy()
@@ -530,7 +534,7 @@ def bench_ll(buf, rank, world, dev, barrier, replays: int = 200):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     barrier()
     # algorithmic floor: per (token, expert) message H + 4H/128 out, 2H back, (W-1)/W remote
-    return {"tokens_per_rank": LL_T, "mode": "fp8 dispatch + bf16 combine, one CUDA graph (5 kernels), replayed",
+    return {"tokens_per_rank": LL_T, "mode": "fp8 dispatch + bf16 combine, one CUDA graph (2 kernels: count+send+wait, push+wait+reduce), replayed",
             "p50_us": float(t[0].item()), "p99_us": float(t[1].item()), "replays": replays, "ep_size": world}
 
 

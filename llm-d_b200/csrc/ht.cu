@@ -615,7 +615,12 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 // the half row in batches of 4 vectors per lane with the loads of up to four source rows in flight
 // together (16 x 16 B per lane).  Accumulation order stays d = 0..W-1.
 constexpr int kRedVec = 4;
-__global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
+// kMaxSrc = ranks the kernel is built for: the 1- and 2-rank builds hold at most 2 x 4 vectors of source
+// data, fit 64 registers and run 4 CTAs per SM (ncu on the generic build at EP=1: 128 registers,
+// 16 warps per SM, issue slots 35 % busy).
+template <int kMaxSrc>
+__global__ void __launch_bounds__(256, kMaxSrc == 1 ? 4 : (kMaxSrc == 2 ? 3 : 2)) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
+  constexpr int kGrp = kMaxSrc < 4 ? kMaxSrc : 4;
   if (a.W > 1) cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W;
@@ -636,9 +641,9 @@ __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_co
                           : stage + ((size_t)t * W + lane) * row_bytes;
     }
     const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-    const char* rows[kMaxRanks];
+    const char* rows[kMaxSrc];
 #pragma unroll
-    for (int d = 0; d < kMaxRanks; ++d)
+    for (int d = 0; d < kMaxSrc; ++d)
       rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
     int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
     for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
@@ -648,11 +653,11 @@ __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_co
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
 #pragma unroll
-      for (int d0 = 0; d0 < kMaxRanks; d0 += 4) {
+      for (int d0 = 0; d0 < kMaxSrc; d0 += kGrp) {
         if ((dmask >> d0) == 0) break;
-        int4 raw[4][kRedVec];
+        int4 raw[kGrp][kRedVec];
 #pragma unroll
-        for (int dd = 0; dd < 4; ++dd) {
+        for (int dd = 0; dd < kGrp; ++dd) {
           if ((dmask >> (d0 + dd)) & 1u) {
 #pragma unroll
             for (int j = 0; j < kRedVec; ++j) {
@@ -662,7 +667,7 @@ __global__ void __launch_bounds__(256, 2) ht_combine_recv_kernel(const __grid_co
           }
         }
 #pragma unroll
-        for (int dd = 0; dd < 4; ++dd) {
+        for (int dd = 0; dd < kGrp; ++dd) {
           if ((dmask >> (d0 + dd)) & 1u) {
 #pragma unroll
             for (int j = 0; j < kRedVec; ++j) {
@@ -1126,8 +1131,9 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
       return B200EP_ERR_ARG;
     }
     const int nsplit = row_bytes / 16 >= 256 ? 2 : 1;
-    const int grid = grid_for(c, T * nsplit, 8, 2);
-    ht_combine_recv_kernel<<<grid, 256, 0, st>>>(a);
+    if (c->world == 1) ht_combine_recv_kernel<1><<<grid_for(c, T * nsplit, 8, 4), 256, 0, st>>>(a);
+    else if (c->world == 2) ht_combine_recv_kernel<2><<<grid_for(c, T * nsplit, 8, 3), 256, 0, st>>>(a);
+    else ht_combine_recv_kernel<kMaxRanks><<<grid_for(c, T * nsplit, 8, 2), 256, 0, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
