@@ -158,7 +158,7 @@ __device__ __forceinline__ void store_pass(const int4 (&raw)[kVpt], int nvec, in
 }
 
 // Quantising passes with 32-byte lanes (KIND == B200EP_X_BF16_QUANT): 4 x 128 x 32 B = 16 KB per pass.
-constexpr int kVpt32 = 4;
+constexpr int kVpt32 = 2;
 __device__ __forceinline__ void load_pass32(const V8* src, int nv32, int v0, int ttid, V8 (&raw)[kVpt32]) {
 #pragma unroll
   for (int u = 0; u < kVpt32; ++u) {
@@ -189,7 +189,7 @@ __device__ __forceinline__ void quant_pass32(const V8 (&raw)[kVpt32], int nv32, 
 // the stage, and warp 0 fans the row out with ONE cp.async.bulk per destination rank while warp 1
 // writes the per-destination metadata.  The next row's loads overlap the bulk copies of this one.
 template <int KIND>
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
+__global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QUANT ? 3 : 2) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
   const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
   const int lane = tid & 31, twarp = ttid >> 5;
@@ -1000,7 +1000,7 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     const size_t stage_bytes = (size_t)(plan.qrow_bytes + 127) / 128 * 128;
     a.nstage = 2 * kTeams * stage_bytes <= 100 * 1024 ? 2 : 1;  // two CTAs per SM must still fit
     const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
-    const int grid = grid_for(c, T, kTeams, 2);
+    const int grid = grid_for(c, T, kTeams, x_kind == B200EP_X_BF16_QUANT ? 3 : 2);
     auto launch = [&](auto kern, int g) -> int {
       B200EP_CUDA(ensure_dynamic_smem((const void*)kern, c->device, (int)smem));
       kern<<<g, kTeams * kTeamThreads, smem, st>>>(a);
