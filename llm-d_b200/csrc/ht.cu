@@ -704,9 +704,12 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
   // CTAs alternate push / reduce-only; push CTAs join the reduction once their rows are out and
   // reduce items are handed out dynamically.  (Measured at EP=8: 1:1 static 483 us, 3:1 502 us --
   // with fewer reducers the reduction falls behind the transfer and becomes a tail.)
-  const int role = blockIdx.x & 1;
+  // Push CTAs take the LOW block indices: blocks are dispatched in index order, so even when the GPU
+  // is shared with other kernels (DBO) every push CTA is resident before any reduce-only CTA can
+  // occupy a slot and spin -- progress of the peers never depends on a CTA that is not running.
   const int nred = gridDim.x >> 1, nsend = gridDim.x - nred;
-  const int ridx = blockIdx.x >> 1;
+  const int role = (int)blockIdx.x < nsend ? 0 : 1;
+  const int ridx = role ? (int)blockIdx.x - nsend : (int)blockIdx.x;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
 
   if (role == 0) {

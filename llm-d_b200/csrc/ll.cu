@@ -111,9 +111,12 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
     return a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + k]
                      : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + k];
   };
+  // fused: block 0 is the count CTA (dispatched first, so the token CTAs that wait for its flags can
+  // never keep it off the GPU), blocks 1.. are token CTAs
   const int ntok_ctas = a.fused ? (int)gridDim.x - 1 : (int)gridDim.x;
+  const int tok_cta = a.fused ? (int)blockIdx.x - 1 : (int)blockIdx.x;
 
-  if (a.fused && (int)blockIdx.x == ntok_ctas) {
+  if (a.fused && blockIdx.x == 0) {
     // ---------------- count role (one CTA): per-expert histogram -> every peer, count flags
     int* s_cnt = reinterpret_cast<int*>(s_mem);
     for (int e = tid; e < a.E; e += blockDim.x) s_cnt[e] = 0;
@@ -135,7 +138,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
     const unsigned long long want_cnt =
         a.fused ? *reinterpret_cast<const volatile unsigned long long*>(a.epoch_data_ptr) + 1 : 0ull;
     bool counts_ready = false;
-    for (int t = blockIdx.x; t < a.T || !counts_ready; t += ntok_ctas) {
+    for (int t = tok_cta; t < a.T || !counts_ready; t += ntok_ctas) {
       const bool have_token = t < a.T;
       if (have_token) {
         if (tid < K) bulk_wait_read0();  // issuing threads: previous copies have read the stage
@@ -193,7 +196,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
           cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt_ptr);
         }
         counts_ready = true;
-        if (blockIdx.x == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
+        if (tok_cta == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
           for (int el = tid; el < e_local; el += blockDim.x) {
             int p = 0;
             for (int s = 0; s < W; ++s) {
@@ -264,6 +267,7 @@ struct LlCombineArgs {
   const float* weights;
   const LlScratch* sc;
   unsigned* done;
+  unsigned* work;  // [3] push queue head, completed blocks, warps finished
   size_t slot_off;
   unsigned long long* epoch_ptr;
   int T, W, me, slot, E, ids_i64, fused;
@@ -275,17 +279,57 @@ __device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a);
 // takes part in the reduction, so the whole combine is one launch.
 __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_constant__ LlCombineArgs a) {
   extern __shared__ __align__(128) char s_mem[];
-  // the epoch this call publishes; read before any CTA can have advanced it (that needs all CTAs to arrive)
+  // the epoch this call publishes; the stored epoch only advances after every warp of the grid has read it
   const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(a.epoch_ptr) + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W, K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
   char* s_row = s_mem + (size_t)warp * row_bytes;
   const int32_t* src_info = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
-  const int total = e_local * cap;
-  for (int idx = blockIdx.x * nwarp + warp; idx < total; idx += gridDim.x * nwarp) {
-    const int el = idx / cap, sl = idx % cap;
-    if (sl >= a.sc->recv_count[el]) continue;
+  // Occupied rows only: exclusive prefix of recv_count over the local experts (one warp, shared memory).
+  __shared__ int s_pref[kMaxLocalExperts + 1];
+  if (warp == 0) {
+    const int per = (e_local + 31) / 32;
+    int sum = 0;
+    for (int i = lane * per; i < min(e_local, (lane + 1) * per); ++i) sum += a.sc->recv_count[i];
+    int incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - sum;
+    for (int i = lane * per; i < min(e_local, (lane + 1) * per); ++i) {
+      s_pref[i] = run;
+      run += a.sc->recv_count[i];
+    }
+    if (lane == 31) s_pref[e_local] = incl;
+  }
+  __syncthreads();
+  const int total = s_pref[e_local];
+  // Rows are handed out from a queue (a.work[0]), eight per CTA per grab (one atomic per CTA, not per
+  // warp), so whichever CTAs are resident do all the pushing; completion is counted in rows
+  // (a.work[1]), not in CTAs.
+  constexpr int kGrab = 8;
+  __shared__ int s_base, s_cta_rows;
+  if (threadIdx.x == 0) s_cta_rows = 0;
+  const int nblocks = total;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = (int)atomicAdd(&a.work[0], (unsigned)kGrab);
+    __syncthreads();
+    const int base = s_base;
+    if (base >= total) break;
+    if (threadIdx.x == 0) s_cta_rows += min(total, base + kGrab) - base;
+    if (warp < kGrab && base + warp < total) {
+      const int r = base + warp;
+      {
+    int lo = 0, hi = e_local - 1;  // largest el with s_pref[el] <= r
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_pref[mid] <= r) lo = mid; else hi = mid - 1;
+    }
+    const int el = lo, sl = r - s_pref[lo];
+    const int idx = el * cap + sl;
     int s = 0;
     while (s + 1 < W && sl >= a.sc->layout_range[(el * W + s + 1) * 2]) ++s;
     if (s == a.me) continue;  // the reduce reads local rows straight from dev_y
@@ -314,9 +358,32 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
       bulk_commit();
     }
     (void)K;
+      }
+    }
   }
   bulk_wait_all();
-  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagLlComb, a.slot, a.me);
+  // all rows this CTA took have landed: add them to the completion count; the CTA that completes the
+  // last row publishes (one system fence); the last CTA of the grid rewinds the queue for the next call
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int done_blocks = s_cta_rows;
+    const unsigned prev = done_blocks ? atom_add_acq_rel_gpu(&a.work[1], (unsigned)done_blocks) : 0u;
+    const bool last_block = done_blocks && prev + done_blocks == (unsigned)nblocks;
+    const unsigned fin = atom_add_acq_rel_gpu(&a.work[2], 1u);  // CTAs that left the push loop
+    if (last_block || (nblocks == 0 && fin == 0)) {
+      fence_acq_rel_sys();
+      for (int d = 0; d < W; ++d)
+        st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagLlComb, a.slot, a.me)), want);
+    }
+    if (fin == gridDim.x - 1) {
+      // every CTA of the grid is past the queue (so each has read the old epoch): rewind the queue
+      // and only now advance the epoch -- a CTA that is scheduled late must still compute `want` right
+      a.work[0] = 0;
+      a.work[1] = 0;
+      a.work[2] = 0;
+      *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = want;
+    }
+  }
   if (a.fused) {
     if ((int)threadIdx.x < W)
       wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagLlComb, a.slot, threadIdx.x)), want,
@@ -542,6 +609,7 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
   a.weights = dev_topk_weights;
   a.sc = reinterpret_cast<LlScratch*>(c->ll_local) + slot;
   a.done = &c->local->done[6 + slot];
+  a.work = &c->local->done[8 + slot * 4];
   a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
   a.T = T;
   a.W = c->world;
