@@ -277,7 +277,7 @@ def main():
     W = world
     # per-slot need: W*T receive rows + T*W stage rows; size the region for it with headroom
     need = 2 * (W * T * (H + H // 32 + K * 12 + 4) + T * W * 2 * H) + (64 << 20)
-    ll_need = b200ep.Buffer.ll_size_hint(LL_T, H, W, E)
+    ll_need = max(b200ep.Buffer.ll_size_hint(256, H, W, E), b200ep.Buffer.ll_size_hint(256, H, W, 288) if 288 % W == 0 else 0)
     sym = int(args.sym_gb * 2**30) if args.sym_gb else int(max(need, ll_need) * 1.1)
     buf = b200ep.Buffer(group, sym_bytes=sym, device=local, rank=rank, world=world)
 
@@ -489,19 +489,37 @@ def main():
 
 
 def bench_ll(buf, rank, world, dev, barrier, replays: int = 200):
-    """128 tokens/rank low-latency dispatch+combine captured in ONE CUDA graph, replayed; per-replay
-    time from CUDA events (max over ranks of the p50 is reported)."""
+    """Low-latency mode (BASELINE.json configs[2] and the 32-256 tokens/rank sweep of configs[4]):
+    dispatch+combine captured in ONE CUDA graph and replayed; per-replay time from CUDA events, max
+    over ranks of the p50.  The headline entry is 128 tokens/rank; `sweep` adds 32/64/256 and the
+    EPLB shape (288 physical experts, 36 per rank at EP=8) when it divides over the ranks."""
+    out = bench_ll_one(buf, rank, world, dev, barrier, LL_T, E, replays)
+    sweep = {}
+    for tok in (32, 64, 256):
+        sweep[f"{tok}"] = bench_ll_one(buf, rank, world, dev, barrier, tok, E, 100, max_tok=256)["p50_us"]
+    if 288 % world == 0:
+        sweep["128_E288"] = bench_ll_one(buf, rank, world, dev, barrier, LL_T, 288, 100)["p50_us"]
+    out["sweep_p50_us"] = sweep
+    return out
+
+
+def bench_ll_one(buf, rank, world, dev, barrier, LL_T, E, replays, max_tok=None):
     import torch.distributed as dist
 
-    x, ids, w = make_inputs(99 + rank, LL_T)
+    max_tok = max_tok or LL_T
+    g0 = torch.Generator().manual_seed(99 + rank)
+    x = (torch.randn(LL_T, H, generator=g0) * (torch.rand(LL_T, 1, generator=g0) * 4)).to(torch.bfloat16)
+    vals, ids = torch.topk(torch.randn(LL_T, E, generator=g0), K, dim=-1, sorted=False)
+    w = torch.softmax(vals, dim=-1).float().contiguous()
+    ids = ids.to(torch.int64).contiguous()
     x, ids, w = x.to(dev), ids.to(dev), w.to(dev)
-    el, cap = E // world, world * LL_T
+    el, cap = E // world, world * max_tok
     y = torch.randn(el, cap, H, device=dev).to(torch.bfloat16)
     out = torch.empty(LL_T, H, dtype=torch.bfloat16, device=dev)
     from b200ep import LlHandle
     from b200ep import _lib as L
 
-    h = LlHandle(0, LL_T, H, K, E, LL_T, True)
+    h = LlHandle(0, LL_T, H, K, E, max_tok, True)
 
     def one():
         buf.ll_dispatch_launch(h, x, ids, False, L.LL_PHASE_ALL)
@@ -534,7 +552,8 @@ def bench_ll(buf, rank, world, dev, barrier, replays: int = 200):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     barrier()
     # algorithmic floor: per (token, expert) message H + 4H/128 out, 2H back, (W-1)/W remote
-    return {"tokens_per_rank": LL_T, "mode": "fp8 dispatch + bf16 combine, one CUDA graph (2 kernels: count+send+wait, push+wait+reduce), replayed",
+    del y
+    return {"tokens_per_rank": LL_T, "experts": E, "max_tokens_per_rank": max_tok, "mode": "fp8 dispatch + bf16 combine, one CUDA graph (2 kernels: count+send+wait, push+wait+reduce), replayed",
             "p50_us": float(t[0].item()), "p99_us": float(t[1].item()), "replays": replays, "ep_size": world}
 
 

@@ -117,3 +117,27 @@ def test_ll_single_launch_paths_single_rank(hook):
             assert np.array_equal(bf16_bits(out), want)
     finally:
         buf.destroy()
+
+
+def test_ll_eplb_expert_count_world8():
+    """guides/wide-ep-lws decode.yaml:114-118 runs with 32 redundant experts: 288 physical experts,
+    36 per rank at EP=8.  Ids are physical ids here (vLLM maps them before the call, deepep_ll.py:291)."""
+    from b200ep import LocalWorld
+
+    W, H, E, K, max_tok = 8, 256, 288, 8, 16
+    world = LocalWorld(W, sym_bytes=64 << 20)
+    try:
+        ins = [make_rank_inputs(max_tok - r, H, E, K, 500 + r) for r in range(W)]
+        xs, ids = [i[0] for i in ins], [i[1] for i in ins]
+        qs = [fp8.group_quant_fp8(bf16_bits(x)) for x in xs]
+        ref = dispatch.ll_dispatch([q for q, _ in qs], [i.numpy() for i in ids], E, max_tok, scales=[s for _, s in qs])
+        res = world.low_latency_dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], max_tok, E, use_fp8=True)
+        for d, (px, ps, cnt, h) in enumerate(res):
+            assert px.shape[0] == 36
+            assert np.array_equal(cnt.cpu().numpy(), ref[d]["recv_count"])
+            pxh = u8(px)
+            for el in range(36):
+                n = int(ref[d]["recv_count"][el])
+                assert np.array_equal(pxh[el, :n], ref[d]["packed_recv_x"][el, :n])
+    finally:
+        world.destroy()
