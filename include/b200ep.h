@@ -168,7 +168,10 @@ int b200ep_ht_dispatch(b200ep_ctx* ctx, int slot, const void* dev_x, const float
 
 /* b200ep_layout + b200ep_ht_notify + b200ep_ht_notify_wait + b200ep_ht_dispatch (all phases) in one
  * host call: the whole of deep_ep.Buffer.get_dispatch_layout + Buffer.dispatch (deepep_ht.py:121-162).
- * The four layout arrays are outputs the caller keeps for the combine. */
+ * The four layout arrays are outputs the caller keeps for the combine.
+ * timeout_ms < 0 selects the HOST-SYNC-FREE form (DeepEP's num_worst_tokens mode): no host wait, the three
+ * host outputs are not written; the number of received rows and the per-expert counts are read on the
+ * device (b200ep_ht_view.rank_prefix[world], .recv_per_expert) and the caller sizes recv views for a worst case. */
 int b200ep_ht_dispatch_all(b200ep_ctx* ctx, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
                            int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
                            int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,

@@ -62,6 +62,8 @@ class HtHandle:
     num_recv: int = -1
     rank_prefix: list[int] = field(default_factory=list)
     keep: Any = None  # tensors that must outlive the asynchronous kernels
+    num_recv_dev: Any = None         # host-sync-free dispatch: rows received, device int32 scalar
+    recv_per_expert_dev: Any = None  # host-sync-free dispatch: per-local-expert counts, device int32 [E/W]
 
 
 @dataclass
@@ -234,11 +236,16 @@ class Buffer:
         return rx, rs, ridx, rw, rsrc
 
     def dispatch(self, x, topk_idx, topk_weights, num_experts: int, *, x_scales=None, quantize: bool = False,
-                 ue8m0: bool = False, layout: Layout | None = None):
+                 ue8m0: bool = False, layout: Layout | None = None, num_worst_tokens: int = 0):
         """Whole high-throughput dispatch (collective).  x: bf16 [T,H] (moved as is, or
         quantised in the kernel when ``quantize``), or e4m3 [T,H] with ``x_scales``.
         Returns (recv_x, recv_x_scales, recv_topk_idx, recv_topk_weights,
-        num_recv_tokens_per_expert_list, handle)."""
+        num_recv_tokens_per_expert_list, handle).
+
+        ``num_worst_tokens > 0`` selects the host-sync-free form (DeepEP's parameter of the same name;
+        SURVEY.md 8(f) f2): nothing waits on the host, the views have ``num_worst_tokens`` rows of which
+        only the first ``handle.num_recv_dev`` (a device scalar) are meaningful, the per-expert list is
+        empty and ``handle.recv_per_expert_dev`` holds the counts on the device."""
         if layout is not None:
             h, args = self._dispatch_prepare(x, topk_idx, topk_weights, num_experts, x_scales, quantize, ue8m0, layout)
             self.ht_notify(h.slot, h.layout)
@@ -263,15 +270,28 @@ class Buffer:
         n = C.c_int()
         pe = (C.c_int32 * el)()
         rp = (C.c_int32 * (self.world + 1))()
+        nosync = num_worst_tokens > 0
         L.check(
             self.lib.b200ep_ht_dispatch_all(
                 self.ctx, slot, _ptr(x), _ptr(x_scales), kind, int(ue8m0), _ptr(topk_idx),
                 int(topk_idx.dtype == torch.int64), _ptr(topk_weights), _ptr(lay.tokens_per_rank),
                 _ptr(lay.tokens_per_expert), _ptr(lay.is_token_in_rank), _ptr(lay.send_off), T, H, K, num_experts,
-                C.byref(n), pe, rp, 120000, _stream()),
+                C.byref(n), pe, rp, -1 if nosync else 120000, _stream()),
             "ht_dispatch_all",
         )
-        h = HtHandle(slot, T, H, K, num_experts, kind, lay, n.value, list(rp), (x, x_scales, topk_idx, topk_weights))
+        keep = (x, x_scales, topk_idx, topk_weights)
+        if nosync:
+            h = HtHandle(slot, T, H, K, num_experts, kind, lay, int(num_worst_tokens), [], keep)
+            v = L.HtView()
+            L.check(self.lib.b200ep_ht_views(self.ctx, slot, C.byref(v)), "ht_views")
+            if num_worst_tokens > v.capacity_rows:
+                raise L.B200EPError(f"num_worst_tokens={num_worst_tokens} exceeds the slot capacity of {v.capacity_rows} rows")
+            devs = self._sym.device
+            prefix = torch.as_tensor(_DevMem(v.rank_prefix, (self.world + 1) * 4), device=devs).view(torch.int32)
+            h.num_recv_dev = prefix[self.world]
+            h.recv_per_expert_dev = torch.as_tensor(_DevMem(v.recv_per_expert, el * 4), device=devs).view(torch.int32)
+            return (*self.ht_views(h)[:4], [], h)
+        h = HtHandle(slot, T, H, K, num_experts, kind, lay, n.value, list(rp), keep)
         return (*self.ht_views(h)[:4], list(pe), h)
 
     def _layout_tensors(self, slot: int, T: int, E: int, dev) -> Layout:

@@ -1157,8 +1157,17 @@ extern "C" int b200ep_ht_dispatch_all(b200ep_ctx* c, int slot, const void* dev_x
   if (rc) return rc;
   rc = b200ep_ht_notify(c, slot, dev_tokens_per_rank, dev_tokens_per_expert, E, B200EP_PHASE_ALL, stream);
   if (rc) return rc;
-  rc = b200ep_ht_notify_wait(c, slot, num_recv_tokens, per_expert, rank_prefix, timeout_ms);
-  if (rc) return rc;
+  if (timeout_ms >= 0) {
+    rc = b200ep_ht_notify_wait(c, slot, num_recv_tokens, per_expert, rank_prefix, timeout_ms);
+    if (rc) return rc;
+  } else {
+    // host-sync-free mode: the caller sized its views for a worst case; counts stay on the device
+    // (b200ep_ht_views: rank_prefix[world] = rows received, recv_per_expert).  Later grids assume the worst.
+    HtPlan plan;
+    rc = make_ht_plan(c, H, K, x_kind, &plan);
+    if (rc) return rc;
+    c->host->num_recv_cache[slot] = plan.cap_rows;
+  }
   return b200ep_ht_dispatch(c, slot, dev_x, dev_x_scales, x_kind, ue8m0, dev_topk_ids, ids_i64, dev_topk_weights,
                             dev_is_token_in_rank, dev_send_off, T, H, K, E, B200EP_PHASE_ALL, stream);
 }

@@ -170,7 +170,8 @@ class Buffer:
         with torch.cuda.stream(self._comm):
             rx, rs, ridx, rw, per_expert, h = self._impl.dispatch(
                 xq.contiguous(), topk_idx.contiguous(), None if topk_weights is None else topk_weights.contiguous(),
-                num_experts, x_scales=xs, layout=lay, quantize=b200ep_quantize, ue8m0=b200ep_ue8m0)
+                num_experts, x_scales=xs, layout=(None if num_worst_tokens > 0 else lay), quantize=b200ep_quantize,
+                ue8m0=b200ep_ue8m0, num_worst_tokens=num_worst_tokens)
         ev = self._leave_comm(compute, async_finish, (xq, xs, topk_idx, topk_weights))
         if expert_alignment > 1:
             per_expert = [(n + expert_alignment - 1) // expert_alignment * expert_alignment for n in per_expert]

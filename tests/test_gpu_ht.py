@@ -156,3 +156,33 @@ def test_ht_one_call_dispatch_single_rank():
             assert np.array_equal(bf16_bits(out), want)
     finally:
         buf.destroy()
+
+
+def test_ht_host_sync_free_dispatch_single_rank():
+    """num_worst_tokens > 0: no host wait; counts stay on the device; first num_recv rows equal the
+    synchronous result and combine gives the same output."""
+    from b200ep import Buffer
+
+    T, H, E, K = 200, 1024, 32, 8
+    buf = Buffer(None, sym_bytes=128 << 20, rank=0, world=1)
+    try:
+        x, ids, w = make_rank_inputs(T, H, E, K, seed=123, mask_frac=0.2)
+        ids[3] = -1  # a token with no expert at all: fewer rows than tokens
+        q, s = fp8.group_quant_fp8(bf16_bits(x))
+        ref = dispatch.ht_dispatch([q], [ids.numpy()], [w.numpy()], E, scales=[s])[0]
+        rx, rs, ridx, rw, per_expert, h = buf.dispatch(x.to(DEV), ids.to(DEV), w.to(DEV), E, quantize=True,
+                                                       num_worst_tokens=T)
+        assert per_expert == [] and rx.shape == (T, H)
+        torch.cuda.synchronize()
+        M = int(h.num_recv_dev)
+        assert M == ref["num_recv_tokens"] and M < T
+        assert np.array_equal(h.recv_per_expert_dev.cpu().numpy(), ref["num_recv_tokens_per_expert"])
+        assert np.array_equal(u8(rx)[:M], ref["recv_x"]) and np.array_equal(ridx.cpu().numpy()[:M], ref["recv_topk_idx"])
+        y = torch.zeros(T, H, dtype=torch.bfloat16, device=DEV)
+        yv = bits.f32_to_bf16(fp8.dequant_fp8(ref["recv_x"], ref["recv_x_scales"]))
+        y[:M] = bits_to_bf16(yv, DEV)
+        out = buf.combine(y, h)
+        want = combine.ht_combine([yv], [ref], [T])[0]
+        assert np.array_equal(bf16_bits(out), want)
+    finally:
+        buf.destroy()
