@@ -140,3 +140,17 @@ def test_ll_roundtrip_identity():
         assert np.abs(bits.bf16_to_f32(outs[s]) - ref).max() <= 1e-2 * max(1.0, np.abs(ref).max())
     q, sc = fp8.group_quant_fp8(xs[0])
     assert np.abs(fp8.dequant_fp8(q, sc) - bits.bf16_to_f32(xs[0])).max() < 0.3
+
+
+def test_fp8_oracle_matches_vllm_cuda_op_golden():
+    """tests/golden/vllm_fp8_quant_gpu.npz was produced on a B200 by vLLM's CUDA quantiser
+    (oracle/gen_golden_gpu.py): the oracle's "div" arithmetic must reproduce its bytes and scales,
+    with and without UE8M0 -- this is what pins SURVEY H1 for the CPU suite."""
+    g = np.load(os.path.join(GOLD, "vllm_fp8_quant_gpu.npz"))
+    for ue in (0, 1):
+        q, s = fp8.group_quant_fp8(g["x"], formula="div", ue8m0=bool(ue))
+        assert np.array_equal(s.view(np.uint32), g[f"s_ue{ue}"].view(np.uint32)), f"scales (ue8m0={ue})"
+        assert np.array_equal(q, g[f"q_ue{ue}"]), f"fp8 bytes (ue8m0={ue})"
+    # and the other two named arithmetics do NOT reproduce it (they are not interchangeable)
+    qr, sr = fp8.group_quant_fp8(g["x"], formula="recip")
+    assert (sr.view(np.uint32) != g["s_ue0"].view(np.uint32)).any()
