@@ -537,7 +537,7 @@ struct HtCombineArgs {
   size_t slot_off;
   unsigned long long* epoch_ptr;
   unsigned* chunk_done;  // [kCombChunks] private counters of the overlapped kernel
-  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished
+  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished, [+1] = role tickets
   unsigned long long epoch_value;  // overlapped kernel only: the epoch this call publishes (host mirror; HT is never graph-captured)
   int T, W, me, slot, nstage;
 };
@@ -704,12 +704,17 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
   // CTAs alternate push / reduce-only; push CTAs join the reduction once their rows are out and
   // reduce items are handed out dynamically.  (Measured at EP=8: 1:1 static 483 us, 3:1 502 us --
   // with fewer reducers the reduction falls behind the transfer and becomes a tail.)
-  // Push CTAs take the LOW block indices: blocks are dispatched in index order, so even when the GPU
-  // is shared with other kernels (DBO) every push CTA is resident before any reduce-only CTA can
-  // occupy a slot and spin -- progress of the peers never depends on a CTA that is not running.
+  // Roles are handed out by a ticket taken when a CTA STARTS: the first nsend CTAs to run push, so even
+  // when the GPU is shared with other kernels (DBO) every push CTA is running before a reduce-only CTA
+  // can occupy a slot and spin -- progress of the peers never depends on a CTA that is not running.
+  // (Splitting by block index instead put all push CTAs on SMs 0..73, i.e. one die: 793 -> 1014 us
+  // per step at EP=8.  Tickets follow the hardware's start order, which interleaves the dies.)
+  __shared__ int s_ticket;
+  if (tid == 0) s_ticket = (int)atomicAdd(&a.red_next[kCombChunks + 1], 1u);
+  __syncthreads();
   const int nred = gridDim.x >> 1, nsend = gridDim.x - nred;
-  const int role = (int)blockIdx.x < nsend ? 0 : 1;
-  const int ridx = role ? (int)blockIdx.x - nsend : (int)blockIdx.x;
+  const int role = s_ticket < nsend ? 0 : 1;
+  const int ridx = role ? s_ticket - nsend : s_ticket;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
 
   if (role == 0) {
@@ -873,7 +878,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
     if (lane == 0) {
       const unsigned prev = atomicAdd(&a.red_next[kCombChunks], 1u);
       if (prev == gridDim.x * nwarp - 1) {
-        for (int c = 0; c <= kCombChunks; ++c) a.red_next[c] = 0;
+        for (int c = 0; c <= kCombChunks + 1; ++c) a.red_next[c] = 0;
       }
     }
   }
