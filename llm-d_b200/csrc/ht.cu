@@ -704,17 +704,39 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
   // CTAs alternate push / reduce-only; push CTAs join the reduction once their rows are out and
   // reduce items are handed out dynamically.  (Measured at EP=8: 1:1 static 483 us, 3:1 502 us --
   // with fewer reducers the reduction falls behind the transfer and becomes a tail.)
-  // Roles are handed out by a ticket taken when a CTA STARTS: the first nsend CTAs to run push, so even
-  // when the GPU is shared with other kernels (DBO) every push CTA is running before a reduce-only CTA
-  // can occupy a slot and spin -- progress of the peers never depends on a CTA that is not running.
-  // (Splitting by block index instead put all push CTAs on SMs 0..73, i.e. one die: 793 -> 1014 us
-  // per step at EP=8.  Tickets follow the hardware's start order, which interleaves the dies.)
-  __shared__ int s_ticket;
-  if (tid == 0) s_ticket = (int)atomicAdd(&a.red_next[kCombChunks + 1], 1u);
-  __syncthreads();
+  // CTAs alternate push / reduce-only by block parity.  Placement matters: putting all push CTAs on
+  // the low block indices (SMs 0..73, one die) cost 793 -> 1014 us per step at EP=8, handing roles out
+  // by start-order tickets 1168 us.  To stay safe when the GPU is shared with other kernels (DBO) and
+  // not every CTA can be resident, a reduce-only CTA first checks that all push CTAs of this rank are
+  // running; if they are not within ~10 us it EXITS (reduce items come from a queue, so the push CTAs
+  // finish the reduction themselves) instead of holding a slot a push CTA may be waiting for.
   const int nred = gridDim.x >> 1, nsend = gridDim.x - nred;
-  const int role = s_ticket < nsend ? 0 : 1;
-  const int ridx = role ? s_ticket - nsend : s_ticket;
+  const int role = blockIdx.x & 1;
+  const int ridx = blockIdx.x >> 1;
+  unsigned* started = &a.red_next[kCombChunks + 1];
+  auto finish = [&]() {  // every warp of the grid, exactly once: the last one rewinds the counters
+    if ((tid & 31) == 0) {
+      const unsigned prev = atomicAdd(&a.red_next[kCombChunks], 1u);
+      if (prev == gridDim.x * (blockDim.x >> 5) - 1)
+        for (int c = 0; c <= kCombChunks + 1; ++c) a.red_next[c] = 0;
+    }
+  };
+  if (role == 0) {
+    if (tid == 0) atomicAdd(started, 1u);
+  } else {
+    __shared__ int s_go;
+    if (tid == 0) {
+      const long long t0 = clock64();
+      while (*reinterpret_cast<volatile unsigned*>(started) < (unsigned)nsend && clock64() - t0 < 20000) {
+      }
+      s_go = *reinterpret_cast<volatile unsigned*>(started) >= (unsigned)nsend;
+    }
+    __syncthreads();
+    if (!s_go) {
+      finish();
+      return;
+    }
+  }
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
 
   if (role == 0) {
@@ -874,13 +896,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kern
         }
       }
     }
-    // the last warp of the whole grid to run out of work rewinds the item counters for the next call
-    if (lane == 0) {
-      const unsigned prev = atomicAdd(&a.red_next[kCombChunks], 1u);
-      if (prev == gridDim.x * nwarp - 1) {
-        for (int c = 0; c <= kCombChunks + 1; ++c) a.red_next[c] = 0;
-      }
-    }
+    finish();  // the last warp of the whole grid to run out of work rewinds the counters for the next call
   }
 }
 
