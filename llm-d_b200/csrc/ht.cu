@@ -12,18 +12,23 @@
 //            every peer's control block and raises a flag; after the wait each
 //            rank knows the whole W x W count matrix, hence the first row it owns
 //            in every destination's receive region (canonical order: source rank
-//            ascending, source token ascending).
-//   dispatch one warp per token: 16-byte loads -> (fp32 amax per 128 group ->
-//            IEEE divide -> e4m3) -> shared memory row -> ONE TMA bulk copy
-//            (cp.async.bulk) per destination rank straight into the peer's receive
-//            region at its final row; top-k ids are rewritten to destination-local
-//            ids on the way.  recv_x is then read in place by the experts.
+//            ascending, source token ascending).  One rank: a single local kernel.
+//   dispatch persistent CTAs of four 128-thread teams, one row per team at a time:
+//            32-byte loads (LDG.E.256), all of a pass in flight -> fp32 amax per
+//            128 group (8-lane shuffles) -> scale by a Markstein-corrected
+//            reciprocal (== IEEE division) -> e4m3 into a double-buffered shared
+//            memory stage -> ONE TMA bulk copy (cp.async.bulk) per destination rank
+//            straight into the peer's receive region at the row's final position;
+//            top-k ids are rewritten to destination-local ids on the way.  recv_x is
+//            then read in place by the experts.
 //   combine  expert ranks push result rows (bf16) with the same staging + bulk copy
-//            into the source rank's stage [token][dst rank]; the source rank sums
-//            the <= W rows of a token in fp32 in rank order and writes bf16 once.
+//            into the source rank's stage [token][dst rank], destinations
+//            interleaved; the source rank sums the <= W rows of a token in fp32 in
+//            rank order and writes bf16 once.  With all phases in one call the push
+//            and the reduction overlap in one kernel (per-chunk flags).
 // Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> CTA barrier ->
-// fence.sys -> CTA counter -> (last CTA) st.release.sys flag in every peer;
-// consumers spin with ld.acquire.sys.
+// atom.acq_rel.gpu on a CTA counter -> (last CTA) ONE fence.acq_rel.sys ->
+// st.relaxed.sys flag in every peer; consumers spin with ld.acquire.sys.
 #include <stdlib.h>
 
 #include "common.cuh"
