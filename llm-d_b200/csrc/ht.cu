@@ -193,13 +193,16 @@ __device__ __forceinline__ void quant_pass32(const V8 (&raw)[kVpt32], int nv32, 
 // 16 KB in flight), waits until its previous TMA bulk copies have read the stage, quantises into
 // the stage, and warp 0 fans the row out with ONE cp.async.bulk per destination rank while warp 1
 // writes the per-destination metadata.  The next row's loads overlap the bulk copies of this one.
-template <int KIND>
+// kH > 0: hidden size known at compile time (the DeepSeek shape), which folds the per-vector bounds
+// checks of the quantising passes; kH == 0: any hidden size.
+template <int KIND, int kH = 0>
 __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QUANT ? 3 : 2) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
   const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
   const int lane = tid & 31, twarp = ttid >> 5;
-  const int W = a.W, K = a.plan.K, H = a.plan.H;
-  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
+  const int W = a.W, K = a.plan.K, H = kH > 0 ? kH : a.plan.H;
+  const int row_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH : a.plan.row_bytes;
+  const int scale_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH / kGroup * 4 : a.plan.scale_bytes;
   const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
   char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
   const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
@@ -1050,7 +1053,8 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
       ht_dispatch_send_warp_kernel<<<grid_for(c, T, kWarpCtaWarps, 1), kWarpCtaWarps * 32, wsmem, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
     } else if (!staged) {
-      if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>, grid);
+      if (x_kind == B200EP_X_BF16_QUANT && H == 7168) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT, 7168>, grid);
+      else if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>, grid);
       else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>, grid);
       else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>, grid);
     } else {
