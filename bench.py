@@ -239,8 +239,8 @@ def run_nccl_agrs(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200ep")
     ap.add_argument("--no-ll", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
