@@ -30,7 +30,7 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-for _p in (ROOT, os.path.join(ROOT, "llm-d_b200")):
+for _p in (ROOT, os.path.join(ROOT, "llm-d_b200"), os.path.join(ROOT, "tests")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
@@ -246,6 +246,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sym-gb", type=float, default=0.0)
     ap.add_argument("--breakdown", action="store_true", help="per-phase CUDA-event breakdown of the step (stderr)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed calls (experiments only)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -280,6 +281,23 @@ def main():
     ll_need = max(b200ep.Buffer.ll_size_hint(256, H, W, E), b200ep.Buffer.ll_size_hint(256, H, W, 288) if 288 % W == 0 else 0)
     sym = int(args.sym_gb * 2**30) if args.sym_gb else int(max(need, ll_need) * 1.1)
     buf = b200ep.Buffer(group, sym_bytes=sym, device=local, rank=rank, world=world)
+
+    # ---- parity first: one untimed step through exactly the calls timed below (Buffer.dispatch + Buffer.combine with
+    # all phases, the host-sync-free pair, graph-replayed low-latency dispatch + combine), every rank's outputs compared
+    # bit for bit with the CPU oracle.  A mismatch aborts the run on every rank: no number without parity.
+    parity_res = None
+    if not args.no_parity:
+        import parity
+
+        try:
+            parity_res = parity.run_bench_parity(buf, group, world, rank, dev, barrier, H=H, E=E, K=K, T_ht=1100, T_ll=LL_T,
+                                                 ll_experts=(E, 288))
+        except parity.ParityError as ex:
+            print(f"[rank {rank}] PARITY FAILED: {ex}", file=sys.stderr, flush=True)
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "n_gpus": world, "parity": {"error": str(ex)[:2000]}}))
+            os._exit(3)
+        barrier()
 
     NBUF = 4  # rotate inputs so a step never finds its inputs in the 126 MB L2
     xs, idss, wss = [], [], []
@@ -509,7 +527,7 @@ def main():
                        "tokens_per_s_per_gpu": value / world},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
             "gpu_launches": steps * (4 if world == 1 else 6) + R * (2 if world == 1 else 4), "ll": ll,
-            "host_sync_free": nosync,
+            "host_sync_free": nosync, "parity": parity_res,
         }
         print(json.dumps(line))
     buf.destroy()

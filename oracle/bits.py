@@ -73,9 +73,32 @@ def f32_to_e4m3(x: np.ndarray) -> np.ndarray:
 def e4m3_to_f32(b: np.ndarray) -> np.ndarray:
     """e4m3fn bit patterns -> float32 (exact); 0x7f / 0xff -> NaN."""
     b = np.ascontiguousarray(b, dtype=np.uint8)
+    if b.size > 4096:  # large inputs: table of the 256 codes, built with the arithmetic below
+        return _e4m3_table()[b]
     s = np.where(b & 0x80, -1.0, 1.0)
     e = ((b >> 3) & 0x0F).astype(np.int64)
     m = (b & 0x07).astype(np.float64)
     v = np.where(e == 0, m * 2.0**-9, (1.0 + m / 8.0) * np.ldexp(1.0, e - 7))
     v = np.where((b & 0x7F) == 0x7F, np.nan, v)
     return (s * v).astype(np.float32)
+
+
+_E4M3_TABLE = None
+
+
+def _e4m3_table() -> np.ndarray:
+    global _E4M3_TABLE
+    if _E4M3_TABLE is None:
+        _E4M3_TABLE = e4m3_to_f32(np.arange(256, dtype=np.uint8))
+    return _E4M3_TABLE
+
+
+def f32_to_e4m3_fast(x: np.ndarray) -> np.ndarray:
+    """Same function as ``f32_to_e4m3`` on non-NaN inputs, through torch's CPU cast
+    (``clamp(x, -448, 448).to(float8_e4m3fn)``), which is multi-threaded.  Used by the
+    full-size parity checks where the pure-numpy version would take minutes;
+    ``tests/test_oracle_bits.py`` holds the two equal on random and adversarial inputs."""
+    import torch
+
+    t = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+    return t.clamp(-E4M3_MAX, E4M3_MAX).to(torch.float8_e4m3fn).view(torch.uint8).numpy()

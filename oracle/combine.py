@@ -79,3 +79,31 @@ def ll_combine(ys, topk_ids, topk_weights, disp, num_experts: int):
                 acc[t] = (acc[t] + prod).astype(np.float32)
         outs.append(f32_to_bf16(acc))
     return outs
+
+
+def ht_combine_source(num_tokens: int, hidden: int, parts):
+    """High-throughput combine as ONE source rank sees it (same arithmetic as ``ht_combine``).
+    parts: one ``(token_idx, y_rows)`` pair per destination rank, ASCENDING rank order: the
+    source tokens that rank received from this source (ascending) and the bf16 rows it sends
+    back for them.  Returns out [num_tokens, hidden] bf16 bits."""
+    acc = np.zeros((num_tokens, hidden), np.float32)
+    for tok, rows in parts:
+        tok = np.asarray(tok, np.int64)
+        if tok.size:
+            acc[tok] = (acc[tok] + bf16_to_f32(np.asarray(rows))).astype(np.float32)
+    return f32_to_bf16(acc)
+
+
+def ll_combine_source(topk_ids, topk_weights, rows, num_experts: int):
+    """Low-latency combine as ONE source rank sees it (same arithmetic as ``ll_combine``).
+    rows: [T, K, H] bf16 bits, rows[t, k] = the expert output row for entry (t, k) (ignored
+    where the id is negative or >= num_experts).  fp32 multiply, then fp32 add, k ascending."""
+    ids = np.asarray(topk_ids).astype(np.int64)
+    w = np.asarray(topk_weights, np.float32)
+    T, K = ids.shape
+    acc = np.zeros((T, np.asarray(rows).shape[2]), np.float32)
+    for k in range(K):
+        m = (ids[:, k] >= 0) & (ids[:, k] < num_experts)
+        prod = (bf16_to_f32(np.asarray(rows)[:, k]) * w[:, k][:, None]).astype(np.float32)
+        acc[m] = (acc[m] + prod[m]).astype(np.float32)
+    return f32_to_bf16(acc)

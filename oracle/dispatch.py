@@ -31,15 +31,19 @@ import numpy as np
 from .layout import dispatch_layout, expert_owner
 
 
-def ht_dispatch(xs, topk_ids, topk_weights, num_experts: int, scales=None):
+def ht_dispatch(xs, topk_ids, topk_weights, num_experts: int, scales=None, dests=None):
     """xs[s]: [T_s, row] payload rows of source rank s (any dtype; copied verbatim).
     scales[s]: optional [T_s, G] float32.  topk_ids[s]: [T_s, K]; topk_weights[s]:
-    [T_s, K] float32.  Returns one dict per destination rank."""
+    [T_s, K] float32.  Returns one dict per destination rank (``None`` for ranks not in
+    ``dests`` when that is given: a rank of a multi-process test only needs its own)."""
     W = len(xs)
     E_local = num_experts // W
     lay = [dispatch_layout(topk_ids[s], num_experts, W) for s in range(W)]
     out = []
     for d in range(W):
+        if dests is not None and d not in dests:
+            out.append(None)
+            continue
         rx, rs, ridx, rw, rsrc = [], [], [], [], []
         prefix = np.zeros(W + 1, np.int64)
         for s in range(W):
@@ -71,16 +75,20 @@ def ht_dispatch(xs, topk_ids, topk_weights, num_experts: int, scales=None):
     return out
 
 
-def ll_dispatch(xs, topk_ids, num_experts: int, max_tokens_per_rank: int, scales=None):
+def ll_dispatch(xs, topk_ids, num_experts: int, max_tokens_per_rank: int, scales=None, dests=None):
     """Low-latency dispatch.  Returns one dict per destination rank with
     packed_recv_x [E_local, W*max_tok, row], optional packed scales, recv_count
     [E_local], src_info [E_local, W*max_tok] (= t*K + k of the source entry, -1 if
-    unused) and layout_range [E_local, W, 2] (start, count per source rank)."""
+    unused) and layout_range [E_local, W, 2] (start, count per source rank).
+    ``dests`` restricts the work to some destination ranks (``None`` elsewhere)."""
     W = len(xs)
     E_local = num_experts // W
     cap = W * max_tokens_per_rank
     out = []
     for d in range(W):
+        if dests is not None and d not in dests:
+            out.append(None)
+            continue
         row = np.asarray(xs[0]).shape[1]
         px = np.zeros((E_local, cap, row), np.asarray(xs[0]).dtype)
         ps = None

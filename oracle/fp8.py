@@ -25,7 +25,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from .bits import E4M3_MAX, bf16_to_f32, f32_to_e4m3
+from .bits import E4M3_MAX, bf16_to_f32, f32_to_e4m3, f32_to_e4m3_fast
 
 EPS = np.float32(1e-10)
 GROUP = 128
@@ -50,11 +50,14 @@ def group_quant_fp8(
     group: int = GROUP,
     formula: str = "div",
     ue8m0: bool = False,
+    fast: bool = False,
 ) -> tuple[np.ndarray, np.ndarray]:
     """Quantise rows of ``x`` in groups of ``group`` elements.
 
     x: [T, H] bf16 bit patterns (uint16) or float32 values.
     Returns (q uint8 [T, H] e4m3fn bit patterns, s float32 [T, H // group]).
+    ``fast`` selects torch's CPU cast for the final fp32 -> e4m3 step (see
+    ``bits.f32_to_e4m3_fast``); everything else is the same numpy arithmetic.
     """
     xf = bf16_to_f32(x) if x_is_bf16_bits else np.ascontiguousarray(x, np.float32)
     T, H = xf.shape
@@ -81,7 +84,7 @@ def group_quant_fp8(
         y = (g * r[:, :, None]).astype(np.float32)
     else:
         raise ValueError(formula)
-    q = f32_to_e4m3(y.reshape(T, H))
+    q = (f32_to_e4m3_fast if fast else f32_to_e4m3)(y.reshape(T, H))
     return q, s
 
 

@@ -186,3 +186,36 @@ def test_ht_host_sync_free_dispatch_single_rank():
         assert np.array_equal(bf16_bits(out), want)
     finally:
         buf.destroy()
+
+
+@pytest.mark.parametrize("ue8m0", [False, True])
+def test_ht_full_size_bit_exact_single_rank(ue8m0):
+    """The instantiation bench.py times at EP=1 -- ht_dispatch_send_kernel<quantise, hidden 7168> through
+    Buffer.dispatch (one C call) -- at the full BASELINE shape (4096 tokens, 256 experts, top-8), byte for
+    byte against oracle/fp8.py + oracle/dispatch.py, then combine against oracle/combine.py; and the received
+    bytes/scales against vLLM's own CUDA quantiser on the same rows (per_token_group_quant_fp8)."""
+    import parity
+    from b200ep import Buffer
+
+    T, H, E, K = 4096, 7168, 256, 8
+    buf = Buffer(None, sym_bytes=1 << 30, rank=0, world=1)
+    try:
+        for it, kind in enumerate(("uniform", "zipf")):
+            parity.check_ht(buf, None, 1, 0, torch.device(DEV), [T - 3 * it], H, E, K, seed=900 + it, dist=kind, ue8m0=ue8m0,
+                            mask_frac=0.05 * it)
+        parity.check_ht(buf, None, 1, 0, torch.device(DEV), [T], H, E, K, seed=910, nosync=True, ue8m0=ue8m0)
+        try:
+            from vllm.model_executor.layers.quantization.utils.fp8_utils import per_token_group_quant_fp8
+        except Exception:  # pragma: no cover
+            per_token_group_quant_fp8 = None
+        if per_token_group_quant_fp8 is not None:
+            x, ids, w = make_rank_inputs(T, H, E, K, seed=920)
+            xd = x.to(DEV)
+            rx, rs, ridx, rw, per_expert, h = buf.dispatch(xd, ids.to(DEV), w.to(DEV), E, quantize=True, ue8m0=ue8m0)
+            vq, vs = per_token_group_quant_fp8(xd, 128, use_ue8m0=ue8m0)
+            torch.cuda.synchronize()
+            assert h.num_recv == T  # one rank, no masked ids: every token, ascending
+            assert torch.equal(rx.view(torch.uint8), vq.view(torch.uint8)), "fp8 bytes differ from vLLM's CUDA op"
+            assert torch.equal(rs.view(torch.int32), vs.contiguous().view(torch.int32)), "scales differ from vLLM's CUDA op"
+    finally:
+        buf.destroy()

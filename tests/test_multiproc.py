@@ -47,3 +47,16 @@ def test_gpu_ipc_world(world):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-6000:]
     for k in range(world):
         assert f"GPU-MP-OK rank {k}/{world}" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gpu_ipc_world_baseline_shapes(world):
+    import torch
+
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    r = _torchrun(world, [WORKER, "gpu_full"], 29671 + world, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-6000:]
+    for k in range(world):
+        assert f"GPU-MP-FULL-OK rank {k}/{world}" in r.stdout
