@@ -104,7 +104,11 @@ int b200ep_set_num_sms(b200ep_ctx* ctx, int num_sms);
  *   dev_send_off          [T,world] int32 out: position of token t among the
  *                         tokens this rank sends to rank d, -1 if it does not
  *                         (exclusive prefix count; makes the receive order
- *                         canonical without atomics).  No DeepEP counterpart. */
+ *                         canonical without atomics).  No DeepEP counterpart.
+ * The kernel keeps its per-call state (block tickets, call epoch, expert histogram) in the context's
+ * private device scratch and rewinds it itself, so the launch takes nothing from host counters and
+ * may be replayed from a CUDA graph; but all calls on ONE context share that scratch: they must not
+ * overlap on the GPU (issue them on one stream, as the deep_ep shim does, or order them with events). */
 int b200ep_layout(b200ep_ctx* ctx, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
                   int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
                   uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream);
@@ -120,7 +124,9 @@ int b200ep_layout(b200ep_ctx* ctx, const void* dev_topk_ids, int ids_i64, int T,
  *   - all calls on a device share that array and each call clears it first, so calls whose
  *     kernels overlap on the GPU race: serialise them (one stream, or external ordering);
  *   - the first call on a device resolves the array's address before launching; make that
- *     first call before any stream capture begins.
+ *     first call before any stream capture begins;
+ *   - call it with the device that owns `stream` current (the address is looked up and cached per
+ *     device ordinal); the cached address does not survive a cudaDeviceReset.
  * `world` is the number of ranks the experts are sharded over (1..B200EP_MAX_RANKS). */
 int b200ep_layout_noalloc(int world, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
                           int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
@@ -168,7 +174,9 @@ int b200ep_ht_dispatch(b200ep_ctx* ctx, int slot, const void* dev_x, const float
 
 /* b200ep_layout + b200ep_ht_notify + b200ep_ht_notify_wait + b200ep_ht_dispatch (all phases) in one
  * host call: the whole of deep_ep.Buffer.get_dispatch_layout + Buffer.dispatch (deepep_ht.py:121-162).
- * The four layout arrays are outputs the caller keeps for the combine.
+ * The four layout arrays are outputs the caller keeps for the combine.  Internally there is no notify launch: the
+ * layout kernel's last block publishes the counts, the dispatch kernel waits for the peers' counts itself, and the
+ * host waits for its row counts only after everything is queued (the wait runs under the dispatch kernel).
  * timeout_ms < 0 selects the HOST-SYNC-FREE form (DeepEP's num_worst_tokens mode): no host wait, the three
  * host outputs are not written; the number of received rows and the per-expert counts are read on the
  * device (b200ep_ht_view.rank_prefix[world], .recv_per_expert) and the caller sizes recv views for a worst case. */
@@ -210,14 +218,19 @@ size_t b200ep_ll_size_hint(int max_tokens_per_rank, int H, int world, int E);
  * COUNT: per-expert counts of this rank's tokens -> all peers.
  * SEND : wait for counts, (quantise,) write each (token, expert) row straight to
  *        its final slot of packed_recv_x on the expert's owner.
- * RECV : wait for all sources (the "hook"). */
+ * RECV : wait for all sources (the "hook").
+ * ue8m0: 0 = fp32 scales; 1 = fp32 scales rounded up to powers of two (DeepEP round_scale);
+ *        2 = the same power-of-two scales as PACKED exponent bytes (DeepEP use_ue8m0; what DeepGEMM reads on
+ *            sm_100, vLLM fp8_utils.py:643-714): b200ep_ll_view.packed_recv_scales is then an int32 array
+ *            [E_local][ceil(H/512)][slots rounded up to 4], byte b of word j = biased exponent of group 4j+b,
+ *            i.e. logical shape [E_local, slots, H/512] with the slot index fastest ("MN-major"). */
 int b200ep_ll_dispatch(b200ep_ctx* ctx, int slot, const void* dev_x_bf16, const void* dev_topk_ids,
                        int ids_i64, int T, int H, int K, int E, int max_tokens_per_rank, int use_fp8,
                        int ue8m0, int phases, void* stream);
 
 typedef struct {
   void* packed_recv_x;        /* [E_local, world*max_tok, H] e4m3 or bf16 */
-  float* packed_recv_scales;  /* [E_local, world*max_tok, H/128] fp32 (NULL if bf16) */
+  float* packed_recv_scales;  /* [E_local, world*max_tok, H/128] fp32 (NULL if bf16); int32 packed UE8M0 if ue8m0 == 2 */
   int32_t* recv_count;        /* [E_local] */
   int32_t* src_info;          /* [E_local, world*max_tok]: t*K+k on the source rank */
   int32_t* layout_range;      /* [E_local, world, 2]: (first slot, count) per source */

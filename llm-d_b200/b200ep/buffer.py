@@ -75,6 +75,7 @@ class LlHandle:
     E: int
     max_tok: int
     use_fp8: bool
+    packed_ue8m0: bool = False  # scales come back as packed exponent bytes (int32, slot index fastest)
     src_info: torch.Tensor | None = None
     layout_range: torch.Tensor | None = None
     keep: Any = None
@@ -375,7 +376,14 @@ class Buffer:
         v = L.LlView()
         L.check(self.lib.b200ep_ll_views(self.ctx, h.slot, C.byref(v)), "ll_views")
         el, cap, H = h.E // self.world, self.world * h.max_tok, h.H
-        if h.use_fp8:
+        if h.use_fp8 and h.packed_ue8m0:
+            # int32 [el, g4, cap4] in memory; handed out as [el, cap, g4] with the slot index fastest -- the
+            # "MN-major, TMA-aligned" layout DeepGEMM wants for packed UE8M0 scales (vLLM fp8_utils.py:643-714)
+            g4, cap4 = (H // 128 + 3) // 4, (cap + 3) // 4 * 4
+            px = self._view(v.packed_recv_x, el * cap * H).view(torch.float8_e4m3fn).view(el, cap, H)
+            ps = self._view(v.packed_recv_scales, el * g4 * cap4 * 4).view(torch.int32).view(el, g4, cap4)
+            ps = ps.permute(0, 2, 1)[:, :cap, :]
+        elif h.use_fp8:
             px = self._view(v.packed_recv_x, el * cap * H).view(torch.float8_e4m3fn).view(el, cap, H)
             ps = self._view(v.packed_recv_scales, el * cap * (H // 128) * 4).view(torch.float32).view(el, cap, H // 128)
         else:
@@ -388,12 +396,17 @@ class Buffer:
         return px, ps, cnt, src, rng
 
     def low_latency_dispatch(self, x, topk_idx, max_tokens_per_rank: int, num_experts: int, *, use_fp8: bool = True,
-                             ue8m0: bool = False, return_recv_hook: bool = False):
-        """Returns (packed_recv_x, packed_recv_scales, recv_count, handle, hook)."""
+                             ue8m0: bool | int = False, return_recv_hook: bool = False):
+        """Returns (packed_recv_x, packed_recv_scales, recv_count, handle, hook).
+        ``ue8m0``: False/0 = fp32 scales, True/1 = fp32 scales rounded up to powers of two,
+        2 = the same scales as packed exponent bytes (int32 view [E_local, slots, H/512], slot index fastest),
+        written by the kernel itself -- like every other output they are complete once the hook has run."""
         assert x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2 and x.is_contiguous()
         assert topk_idx.is_contiguous() and topk_idx.shape[0] == x.shape[0]
         T, H = x.shape
-        h = LlHandle(self.next_slot(), T, H, topk_idx.shape[1], num_experts, max_tokens_per_rank, use_fp8)
+        ue8m0 = int(ue8m0)
+        h = LlHandle(self.next_slot(), T, H, topk_idx.shape[1], num_experts, max_tokens_per_rank, use_fp8,
+                     packed_ue8m0=(use_fp8 and ue8m0 == 2))
         h.keep = (x, topk_idx)
         first = L.LL_PHASE_COUNT | L.LL_PHASE_SEND
         self.ll_dispatch_launch(h, x, topk_idx, ue8m0, first if return_recv_hook else L.LL_PHASE_ALL)
@@ -482,7 +495,8 @@ class LocalWorld:
         hs = []
         for r in range(W):
             T, H = xs[r].shape
-            hs.append(LlHandle(self.bufs[r].next_slot(), T, H, topk_idx[r].shape[1], num_experts, max_tok, use_fp8))
+            hs.append(LlHandle(self.bufs[r].next_slot(), T, H, topk_idx[r].shape[1], num_experts, max_tok, use_fp8,
+                               packed_ue8m0=(use_fp8 and int(ue8m0) == 2)))
         for ph in (L.LL_PHASE_COUNT, L.LL_PHASE_SEND, L.LL_PHASE_RECV):
             for r in range(W):
                 self.bufs[r].ll_dispatch_launch(hs[r], xs[r], topk_idx[r], ue8m0, ph)

@@ -71,6 +71,7 @@ struct HtPlan {
 struct LlPlan {
   size_t off_x, off_scales, off_src, off_stage;
   int cap;  // world * max_tok slots per local expert
+  int g4, cap4;  // packed-UE8M0 scales: int32 [e_local][g4 = ceil(H/512)][cap4 = cap rounded up to 4]
   int e_local;
   int row_bytes, scale_bytes;
   int H, K, max_tok, use_fp8;
@@ -136,6 +137,38 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 // all of this thread's groups are complete (writes performed)
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// at most N of this thread's most recent groups still pending (reading / at all)
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+// TMA bulk copy global -> shared, completion (bytes) signalled on an mbarrier of this CTA
+__device__ __forceinline__ void bulk_g2s(void* sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(sdst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 // order this thread's generic-proxy shared-memory writes before later async-proxy (TMA) reads
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -274,28 +307,38 @@ __device__ __forceinline__ float group_amax8(float m) {
   m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
   return m;
 }
-// quantise the 16 bf16 values of `v` with the scale of their group -> 16 e4m3 bytes
+// |x| maximum over the 16 bf16 values of `v`.  Done on packed bf16 pairs (HMNMX2 with |.| operands:
+// a bf16 maximum is exact, NaNs are skipped as fmaxf does), widened to fp32 once at the end:
+// ~18 instructions instead of ~48 for unpack + fabs + fmax per element.
 __device__ __forceinline__ float absmax16(const V8& v) {
-  float m = 0.f;
+  __nv_bfloat162 m = __habs2(*reinterpret_cast<const __nv_bfloat162*>(&v.w[0]));
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    m = fmaxf(m, fabsf(__uint_as_float(v.w[i] << 16)));
-    m = fmaxf(m, fabsf(__uint_as_float(v.w[i] & 0xffff0000u)));
-  }
-  return m;
+  for (int i = 1; i < 8; ++i) m = __hmax2(m, __habs2(*reinterpret_cast<const __nv_bfloat162*>(&v.w[i])));
+  const uint32_t u = *reinterpret_cast<const uint32_t*>(&m);
+  return fmaxf(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
 }
+// Quantise the 16 bf16 values of `v` with the scale of their group -> 16 e4m3 bytes.
+// x / s by Markstein's correction (see div_by_scale) on PAIRS of values with the packed fp32
+// instructions of sm_100 (FMUL2 / FFMA2, round to nearest per lane, i.e. the same results as the
+// scalar forms): q0 = x*r, e = fma(q0, -s, x), q = fma(e, r, q0).  The sign of a zero quotient
+// (x = -0, or an underflowing negative x) is restored on the e4m3 bytes instead of with one
+// copysign per value: byte |= sign bit of the source bf16.
 __device__ __forceinline__ uint4 quant16(const V8& v, float s) {
   const float r = __frcp_rn(s);
+  const float2 r2 = make_float2(r, r), ns2 = make_float2(-s, -s);
   uint32_t o[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const float f0 = __uint_as_float(v.w[2 * i] << 16), f1 = __uint_as_float(v.w[2 * i] & 0xffff0000u);
-    const float f2 = __uint_as_float(v.w[2 * i + 1] << 16), f3 = __uint_as_float(v.w[2 * i + 1] & 0xffff0000u);
-    const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(div_by_scale(f0, s, r), div_by_scale(f1, s, r)),
-                                                 __NV_SATFINITE, __NV_E4M3);
-    const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(div_by_scale(f2, s, r), div_by_scale(f3, s, r)),
-                                                 __NV_SATFINITE, __NV_E4M3);
-    o[i] = lo | (hi << 16);
+    const uint32_t wa = v.w[2 * i], wb = v.w[2 * i + 1];
+    const float2 a = make_float2(__uint_as_float(wa << 16), __uint_as_float(wa & 0xffff0000u));
+    const float2 b = make_float2(__uint_as_float(wb << 16), __uint_as_float(wb & 0xffff0000u));
+    const float2 qa0 = __fmul2_rn(a, r2), qb0 = __fmul2_rn(b, r2);
+    const float2 qa = __ffma2_rn(__ffma2_rn(qa0, ns2, a), r2, qa0);
+    const float2 qb = __ffma2_rn(__ffma2_rn(qb0, ns2, b), r2, qb0);
+    const uint32_t lo = __nv_cvt_float2_to_fp8x2(qa, __NV_SATFINITE, __NV_E4M3);
+    const uint32_t hi = __nv_cvt_float2_to_fp8x2(qb, __NV_SATFINITE, __NV_E4M3);
+    // sign bytes: bf16 sign bits live in bytes 1 and 3 of each source word
+    o[i] = (lo | (hi << 16)) | (__byte_perm(wa, wb, 0x7531) & 0x80808080u);
   }
   return make_uint4(o[0], o[1], o[2], o[3]);
 }
@@ -330,10 +373,17 @@ cudaError_t ensure_dynamic_smem(const void* kernel, int device, int bytes);
 // Private scratch layout (device memory owned by the context, not peer visible)
 namespace b200ep {
 constexpr int kMaxLayoutBlocks = 1024;
+constexpr int kMaxExperts = kMaxRanks * kMaxLocalExperts;
 struct LocalScratch {
   unsigned done[64];                                         // CTA-completion counters, one per kernel family
-  unsigned long long layout_ticket;                          // monotonically increasing block ticket
+  // routing-layout kernel: all of it lives on the device and is rewound by the kernel's last block,
+  // so the launch takes no per-call host counter (replays under a CUDA graph)
+  unsigned long long layout_ticket;                          // next logical block id of the running call
+  unsigned layout_done;                                      // blocks of the running call that have finished
+  unsigned layout_pad;
+  unsigned long long layout_epoch;                           // calls completed so far (tags layout_pub)
   unsigned long long layout_pub[kMaxLayoutBlocks][kMaxRanks]; // (epoch << 32 | count) per block and rank
+  int layout_hist[kMaxExperts];                              // per-expert totals of the running call, zero between calls
   HtMeta ht[kNumSlots];
   unsigned long long epoch[kNumFlagCat][kNumSlots];          // call epochs, advanced on the device
 };
@@ -363,7 +413,6 @@ struct b200ep_ctx {
   b200ep::HostMirror* host;      // pinned, mapped
   b200ep::HostMirror* host_dev;  // device alias of `host`
   uint64_t epoch[b200ep::kNumFlagCat][b200ep::kNumSlots];
-  uint64_t layout_epoch, layout_ticket_base;
   b200ep::HtPlan ht_plan[b200ep::kNumSlots];
   b200ep::LlPlan ll_plan[b200ep::kNumSlots];
   int ht_e_local[b200ep::kNumSlots];  // E/world of the last notify on the slot

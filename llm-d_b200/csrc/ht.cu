@@ -9,90 +9,48 @@
 //
 // Data path (no ring buffers, no receiver-side copy):
 //   notify   every rank writes its per-destination and per-expert counts into
-//            every peer's control block and raises a flag; after the wait each
-//            rank knows the whole W x W count matrix, hence the first row it owns
-//            in every destination's receive region (canonical order: source rank
-//            ascending, source token ascending).  One rank: a single local kernel.
-//   dispatch persistent CTAs of four 128-thread teams, one row per team at a time:
-//            32-byte loads (LDG.E.256), all of a pass in flight -> fp32 amax per
-//            128 group (8-lane shuffles) -> scale by a Markstein-corrected
-//            reciprocal (== IEEE division) -> e4m3 into a double-buffered shared
-//            memory stage -> ONE TMA bulk copy (cp.async.bulk) per destination rank
-//            straight into the peer's receive region at the row's final position;
-//            top-k ids are rewritten to destination-local ids on the way.  recv_x is
-//            then read in place by the experts.
-//   combine  expert ranks push result rows (bf16) with the same staging + bulk copy
-//            into the source rank's stage [token][dst rank], destinations
-//            interleaved; the source rank sums the <= W rows of a token in fp32 in
-//            rank order and writes bf16 once.  With all phases in one call the push
-//            and the reduction overlap in one kernel (per-chunk flags).
-// Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> CTA barrier ->
-// atom.acq_rel.gpu on a CTA counter -> (last CTA) ONE fence.acq_rel.sys ->
-// st.relaxed.sys flag in every peer; consumers spin with ld.acquire.sys.
-#include <stdlib.h>
-
-#include "common.cuh"
+//            every peer's control block and raises a flag (notify.cuh).  On the
+//            production path this is the tail of the routing-layout kernel and the
+//            prologue of the dispatch kernel: no launch of its own.
+//   dispatch W > 1: persistent CTAs of four 128-thread teams, one row per team at a
+//            time: 32-byte loads (LDG.E.256), all of a pass in flight -> fp32 amax per
+//            128 group (8-lane shuffles) -> scale by a Markstein-corrected reciprocal
+//            (== IEEE division, packed FFMA2) -> e4m3 into a double-buffered shared
+//            memory stage -> TMA bulk copies (cp.async.bulk) per destination rank
+//            straight into the peer's receive region at the row's final position
+//            (payload, scales, and the per-destination top-k ids / weights rows,
+//            which are staged in shared memory too).
+//            W == 1: nothing crosses a link, so rows go from registers straight to
+//            the receive region (no staging, no barriers; HBM-bound).
+//   combine  expert ranks return result rows (bf16).  The rows a rank received from
+//            source s are contiguous in its receive order, and they land on s in
+//            the same order in stage[dst rank][send position]: the push is a
+//            software DMA -- one thread per CTA drives TMA loads (global -> shared)
+//            and TMA stores (shared -> peer) of multi-row pieces through a 4-stage
+//            ring, no data touches registers.  The source rank sums the <= W rows
+//            of a token in fp32 in rank order and writes bf16 once.  With all
+//            phases in one call every CTA does both: thread 0 drives the DMA, the
+//            other warps reduce chunks of 512 tokens as their per-chunk flags come up.
+// Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> atom.acq_rel.gpu
+// on a counter -> (last arrival) ONE fence.acq_rel.sys -> st.relaxed.sys flag in
+// every peer; consumers spin with ld.acquire.sys.
+#include "notify.cuh"
 
 namespace b200ep {
 
-// ------------------------------------------------------------------ notify
+// ------------------------------------------------------------------ notify (phase-by-phase callers)
 __global__ void __launch_bounds__(256)
     ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, const int32_t* __restrict__ tok_per_rank,
                           const int32_t* __restrict__ tok_per_expert, unsigned long long* epoch_ptr) {
-  for (int d = 0; d < W; ++d) {
-    char* ctrl = peers.base[d];
-    int32_t* cr = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntRankOff) + ((size_t)slot * kMaxRanks + me) * kMaxRanks;
-    int32_t* ce = reinterpret_cast<int32_t*>(ctrl + kCtrlHtCntExpOff) + ((size_t)slot * kMaxRanks + me) * kMaxLocalExperts;
-    if ((int)threadIdx.x < W) cr[threadIdx.x] = tok_per_rank[threadIdx.x];
-    for (int i = threadIdx.x; i < e_local; i += blockDim.x) ce[i] = tok_per_expert[d * e_local + i];
-  }
-  single_cta_signal(epoch_ptr, peers, W, kFlagHtNotify, slot, me);
-}
-
-// Derive this rank's receive offsets / totals from the count matrix and post them to the host.
-// counts come from the control block (filled by every rank's notify_send) or, for a single rank,
-// straight from the layout arrays (no exchange, no flags, no fence).
-__device__ __forceinline__ void notify_finish(const int32_t* cr, int cr_stride, const int32_t* ce, int ce_stride, int W,
-                                              int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
-                                              unsigned long long epoch) {
-  const int tid = threadIdx.x;
-  volatile unsigned long long* hw = host->word[slot];
-  if (tid == 0) {
-    int p = 0;
-    for (int s = 0; s < W; ++s) {
-      meta->rank_prefix[s] = p;
-      hw[1 + s] = host_word(epoch, p);
-      p += __ldcg(&cr[s * cr_stride + me]);
-    }
-    meta->rank_prefix[W] = p;
-    hw[1 + W] = host_word(epoch, p);
-    meta->num_recv = p;
-    hw[0] = host_word(epoch, p);
-  }
-  if (tid >= 32 && tid < 32 + W) {
-    const int d = tid - 32;
-    int b = 0;
-    for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * cr_stride + d]);
-    meta->send_base[d] = b;
-    meta->send_count[d] = __ldcg(&cr[me * cr_stride + d]);
-  }
-  for (int i = tid; i < e_local; i += blockDim.x) {
-    int n = 0;
-    for (int s = 0; s < W; ++s) n += __ldcg(&ce[(size_t)s * ce_stride + i]);
-    meta->recv_per_expert[i] = n;
-    hw[1 + kMaxRanks + 1 + i] = host_word(epoch, n);
-  }
+  notify_publish(peers, W, me, slot, e_local, tok_per_rank, tok_per_expert, epoch_ptr);
 }
 
 __global__ void __launch_bounds__(256)
     ht_notify_recv_kernel(const char* my_base, int W, int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
                           const unsigned long long* epoch_ptr) {
   cta_wait_all_sources(my_base, W, kFlagHtNotify, slot, me, epoch_ptr);
-  const int32_t* cr = reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntRankOff) + (size_t)slot * kMaxRanks * kMaxRanks;
-  const int32_t* ce =
-      reinterpret_cast<const int32_t*>(my_base + kCtrlHtCntExpOff) + (size_t)slot * kMaxRanks * kMaxLocalExperts;
-  notify_finish(cr, kMaxRanks, ce, kMaxLocalExperts, W, me, slot, e_local, meta, host,
-                *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr));
+  notify_finish(ctrl_cnt_rank(my_base, slot), kMaxRanks, ctrl_cnt_expert(my_base, slot), kMaxLocalExperts, W, me, slot,
+                e_local, meta, host, *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr));
 }
 
 // world == 1: the whole count "exchange" in one small kernel.
@@ -115,11 +73,15 @@ struct HtDispatchArgs {
   const float* weights;
   const uint8_t* in_rank;
   const int32_t* send_off;
-  const HtMeta* meta;
+  HtMeta* meta;
+  HostMirror* host;
   unsigned* done;
   size_t slot_off;  // kCtrlBytes + slot * slot_bytes
-  unsigned long long* epoch_ptr;
+  unsigned long long* epoch_ptr;                  // data flags
+  const unsigned long long* notify_epoch_ptr;     // count flags (prologue)
   int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
+  int prologue;   // 1: wait for the peers' counts and derive the offsets here (no notify-recv launch)
+  int meta_bulk;  // 1: top-k ids / weights rows travel as TMA bulk copies too (K % 4 == 0)
 };
 
 constexpr int kTeamThreads = 128;  // a team of 4 warps moves one row at a time
@@ -138,31 +100,15 @@ __device__ __forceinline__ void load_pass(const int4* src, int nvec, int v0, int
     raw[u] = v < nvec ? ld_nc_v4(src + v) : make_int4(0, 0, 0, 0);
   }
 }
-
-// Registers -> shared-memory stage; KIND B200EP_X_BF16_QUANT quantises on the way
-// (16 consecutive lanes x 8 bf16 = one 128-element group).
-template <int KIND>
-__device__ __forceinline__ void store_pass(const int4 (&raw)[kVpt], int nvec, int v0, int ttid, char* s_row,
-                                           float* s_scale, bool ue8m0) {
+__device__ __forceinline__ void store_pass(const int4 (&raw)[kVpt], int nvec, int v0, int ttid, char* s_row) {
 #pragma unroll
   for (int u = 0; u < kVpt; ++u) {
     const int v = v0 + u * kTeamThreads + ttid;
-    if (v0 + u * kTeamThreads >= nvec) break;  // uniform over the team
-    if (KIND == B200EP_X_BF16_QUANT) {
-      float f[8];
-      unpack8(raw[u], f);
-      const float s = group_scale(group_amax16(absmax8(f)), ue8m0);
-      if (v < nvec) {
-        *reinterpret_cast<uint2*>(s_row + (size_t)v * 8) = quant8(f, s);
-        if ((ttid & 15) == 0) s_scale[v >> 4] = s;
-      }
-    } else {
-      if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
-    }
+    if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
   }
 }
 
-// Quantising passes with 32-byte lanes (KIND == B200EP_X_BF16_QUANT): 4 x 128 x 32 B = 16 KB per pass.
+// Quantising passes with 32-byte lanes (KIND == B200EP_X_BF16_QUANT): 2 x 128 x 32 B = 8 KB per pass.
 constexpr int kVpt32 = 2;
 __device__ __forceinline__ void load_pass32(const V8* src, int nv32, int v0, int ttid, V8 (&raw)[kVpt32]) {
 #pragma unroll
@@ -189,38 +135,73 @@ __device__ __forceinline__ void quant_pass32(const V8 (&raw)[kVpt32], int nv32, 
   }
 }
 
+__device__ __forceinline__ long long load_topk_id(const void* ids, int ids_i64, size_t i) {
+  return ids_i64 ? reinterpret_cast<const long long*>(ids)[i] : (long long)reinterpret_cast<const int*>(ids)[i];
+}
+
 // Persistent CTAs of four 128-thread teams.  Per row a team: issues every load of the row (up to
 // 16 KB in flight), waits until its previous TMA bulk copies have read the stage, quantises into
-// the stage, and warp 0 fans the row out with ONE cp.async.bulk per destination rank while warp 1
-// writes the per-destination metadata.  The next row's loads overlap the bulk copies of this one.
+// the stage (warp 1 also builds the per-destination top-k rows there), and warp 0 fans the row out:
+// lane d issues the bulk copies for destination rank d.  The next row's loads overlap the copies.
 // kH > 0: hidden size known at compile time (the DeepSeek shape), which folds the per-vector bounds
 // checks of the quantising passes; kH == 0: any hidden size.
 template <int KIND, int kH = 0>
-__global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QUANT ? 3 : 2) ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
+__global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QUANT ? 3 : 2)
+    ht_dispatch_send_kernel(const __grid_constant__ HtDispatchArgs a) {
   extern __shared__ __align__(128) char s_mem[];
+  __shared__ int s_send_base[kMaxRanks];
   const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
   const int lane = tid & 31, twarp = ttid >> 5;
   const int W = a.W, K = a.plan.K, H = kH > 0 ? kH : a.plan.H;
   const int row_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH : a.plan.row_bytes;
   const int scale_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH / kGroup * 4 : a.plan.scale_bytes;
-  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
+  const int meta_off = (row_bytes + scale_bytes + 15) / 16 * 16;
+  const int stage_bytes = (meta_off + (a.meta_bulk ? W * K * 12 : 0) + 127) / 128 * 128;
   char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
   const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
   const int nvec = in_row_bytes / 16;
+  const char* my_base = a.peers.base[a.me];
   int n = 0;  // rows this team has staged so far: stage = n % nstage, one bulk group per row and lane
+
+  if (a.prologue) {
+    // the peers' counts of THIS call (their layout kernels published them; ours did too, which is
+    // what advanced *notify_epoch_ptr): wait, then every CTA derives its own send offsets
+    cta_wait_all_sources(my_base, W, kFlagHtNotify, a.slot, a.me, a.notify_epoch_ptr);
+    const int32_t* cr = ctrl_cnt_rank(my_base, a.slot);
+    if (tid < W) {
+      int b = 0;
+      for (int s = 0; s < a.me; ++s) b += __ldcg(&cr[s * kMaxRanks + tid]);
+      s_send_base[tid] = b;
+    }
+    if (blockIdx.x == 0)  // receive-side bookkeeping and the host mirror (the host may be waiting for it)
+      notify_finish(cr, kMaxRanks, ctrl_cnt_expert(my_base, a.slot), kMaxLocalExperts, W, a.me, a.slot, a.e_local, a.meta,
+                    a.host, *reinterpret_cast<const volatile unsigned long long*>(a.notify_epoch_ptr));
+  } else if (tid < W) {
+    s_send_base[tid] = a.meta->send_base[tid];
+  }
+  __syncthreads();
 
   for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
     // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
     int my_in = 0, my_row = -1;
     if (lane < W) {
       my_in = a.in_rank[(size_t)t * W + lane];
-      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
+      if (my_in) my_row = s_send_base[lane] + a.send_off[(size_t)t * W + lane];
     }
     const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
     if (dmask == 0) continue;  // uniform over the team
 
+    // warp 1: this token's top-k ids and weights (loads in flight with the row)
+    long long id = -1;
+    float w = 0.f;
+    if (twarp == 1 && lane < K) {
+      id = load_topk_id(a.ids, a.ids_i64, (size_t)t * K + lane);
+      w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+    }
+
     char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
     float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
+    char* s_meta = s_row + meta_off;
     ++n;
     if (KIND == B200EP_X_BF16_QUANT) {
       const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
@@ -232,7 +213,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
       }
       team_bar(team);
       quant_pass32(raw, nv32, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
-      for (int v0 = kTeamThreads * kVpt32; v0 < nv32; v0 += kTeamThreads * kVpt32) {  // rows wider than 16 KB
+      for (int v0 = kTeamThreads * kVpt32; v0 < nv32; v0 += kTeamThreads * kVpt32) {  // rows wider than 8 KB
         load_pass32(src, nv32, v0, ttid, raw);
         quant_pass32(raw, nv32, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
       }
@@ -244,15 +225,38 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
         if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
       }
       team_bar(team);
-      store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, false);
+      store_pass(raw, nvec, 0, ttid, s_row);
       for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
         load_pass(src, nvec, v0, ttid, raw);
-        store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, false);
+        store_pass(raw, nvec, v0, ttid, s_row);
       }
     }
     if (KIND == B200EP_X_FP8) {
       const int ng = H / kGroup;
       for (int g = ttid; g < ng; g += kTeamThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
+    }
+    if (twarp == 1) {
+      // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
+      const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
+      for (int d = 0; d < W; ++d) {
+        if (!((dmask >> d) & 1u)) continue;
+        const bool mine = owner == d;
+        const long long lid = mine ? id - (long long)d * a.e_local : -1;
+        const float lw = mine ? w : 0.f;
+        if (a.meta_bulk) {
+          if (lane < K) {
+            reinterpret_cast<long long*>(s_meta)[d * K + lane] = lid;
+            reinterpret_cast<float*>(s_meta + (size_t)W * K * 8)[d * K + lane] = lw;
+          }
+        } else {
+          const int row = __shfl_sync(0xffffffffu, my_row, d);
+          if (lane < K) {
+            char* dst = a.peers.base[d] + a.slot_off;
+            reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = lid;
+            reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = lw;
+          }
+        }
+      }
     }
     fence_proxy_async_smem();
     team_bar(team);
@@ -262,6 +266,10 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
         bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
         if (scale_bytes && (scale_bytes & 15) == 0)
           bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
+        if (a.meta_bulk) {
+          bulk_s2g(dst + a.plan.off_idx + (size_t)my_row * K * 8, s_meta + (size_t)lane * K * 8, K * 8);
+          bulk_s2g(dst + a.plan.off_w + (size_t)my_row * K * 4, s_meta + (size_t)W * K * 8 + (size_t)lane * K * 4, K * 4);
+        }
         *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
       }
       bulk_commit();  // every lane, every row (possibly empty): group count == rows staged
@@ -275,256 +283,63 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
         }
         __syncwarp();
       }
-    } else if (twarp == 1) {
-      // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
-      long long id = -1;
-      float w = 0.f;
-      if (lane < K) {
-        id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
-                       : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
-        w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
-      }
-      const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
-      for (int d = 0; d < W; ++d) {
-        if (!((dmask >> d) & 1u)) continue;
-        const int row = __shfl_sync(0xffffffffu, my_row, d);
-        if (lane < K) {
-          char* dst = a.peers.base[d] + a.slot_off;
-          const bool mine = owner == d;
-          reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
-          reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
-        }
-      }
     }
   }
   if ((ttid >> 5) == 0) bulk_wait_all();
   if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);  // a single rank has nobody to tell
 }
 
-// ---- warp-granular quantising dispatch (KIND == B200EP_X_BF16_QUANT, rows up to 8192 elements).
-// ncu on the team kernel at EP=1: 21 % of the stall samples were team barriers and 24 % first uses of
-// loaded data, issue slots 56 % busy.  Here every warp owns whole rows and a private shared-memory
-// stage, so nothing but __syncwarp separates load -> quantise -> TMA fan-out, and 24 independent
-// warps per SM (one 768-thread CTA, <= 85 registers) keep 4 x 32 B x 32 lanes each in flight.
-constexpr int kWarpCtaWarps = 24;
-__global__ void __launch_bounds__(kWarpCtaWarps * 32, 1) ht_dispatch_send_warp_kernel(const __grid_constant__ HtDispatchArgs a) {
-  extern __shared__ __align__(128) char s_mem[];
+// ---- world == 1, quantising kind: rows never leave the GPU, so there is nothing to stage.
+// A warp takes (row, segment of up to 4 x 512 values): four 32-byte loads per lane in flight, the
+// 128-value group is 8 lanes (3 shuffles), e4m3 bytes go out as one 16-byte store per lane (512
+// contiguous bytes per warp) and the group's scale from its first lane.  No shared memory, no
+// barriers: the kernel is bound by HBM (2H in, H + 4H/128 out per token).
+constexpr int kLocalU = 4;
+template <int kH, bool kUe8m0>
+__global__ void __launch_bounds__(256, 3) ht_dispatch_local_kernel(const __grid_constant__ HtDispatchArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int W = a.W, K = a.plan.K, H = a.plan.H;
-  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
-  const int stage_bytes = (row_bytes + scale_bytes + 127) / 128 * 128;
-  char* s_row = s_mem + (size_t)warp * stage_bytes;
-  float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
-  const int nv32 = H / 16;
-  const bool ue8m0 = a.ue8m0 != 0;
-
-  for (int t = blockIdx.x * kWarpCtaWarps + warp; t < a.T; t += gridDim.x * kWarpCtaWarps) {
-    int my_in = 0, my_row = -1;
-    if (lane < W) {
-      my_in = a.in_rank[(size_t)t * W + lane];
-      if (my_in) my_row = a.meta->send_base[lane] + a.send_off[(size_t)t * W + lane];
-    }
-    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
-    if (dmask == 0) continue;
+  const int H = kH > 0 ? kH : a.plan.H, K = a.plan.K;
+  const int nv32 = H / 16, ng = H / kGroup;
+  const int nseg = (nv32 + 32 * kLocalU - 1) / (32 * kLocalU);
+  char* base = a.peers.base[a.me] + a.slot_off;
+  uint4* out_x = reinterpret_cast<uint4*>(base + a.plan.off_x);
+  float* out_s = reinterpret_cast<float*>(base + a.plan.off_scales);
+  const long long items = (long long)a.T * nseg;
+  for (long long it = (long long)blockIdx.x * 8 + warp; it < items; it += (long long)gridDim.x * 8) {
+    const int t = (int)(it / nseg), seg = (int)(it % nseg);
+    const int row = __ldg(a.send_off + t);  // world 1: the token's row, -1 if it has no valid expert
     const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
-    bool stage_free = false;
-    for (int v0 = 0; v0 < nv32; v0 += 32 * kVpt32) {
-      V8 raw[kVpt32];
+    V8 raw[kLocalU];
 #pragma unroll
-      for (int u = 0; u < kVpt32; ++u) {
-        const int v = v0 + u * 32 + lane;
-        if (v < nv32) raw[u] = ld_nc_v8(src + v);
-        else {
+    for (int u = 0; u < kLocalU; ++u) {
+      const int v = (seg * kLocalU + u) * 32 + lane;
+      if (v < nv32) raw[u] = ld_nc_v8(src + v);
+      else {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
-        }
-      }
-      if (!stage_free) {  // loads are in flight; now make sure the previous row's copies have read the stage
-        bulk_wait_read0();
-        __syncwarp();
-        stage_free = true;
-      }
-#pragma unroll
-      for (int u = 0; u < kVpt32; ++u) {
-        const int v = v0 + u * 32 + lane;
-        if (v0 + u * 32 >= nv32) break;  // uniform over the warp
-        const float s = group_scale(group_amax8(absmax16(raw[u])), ue8m0);
-        if (v < nv32) {
-          reinterpret_cast<uint4*>(s_row)[v] = quant16(raw[u], s);
-          if ((lane & 7) == 0) s_scale[v >> 3] = s;
-        }
+        for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
       }
     }
-    fence_proxy_async_smem();
-    __syncwarp();
-    if (my_in) {
-      char* dst = a.peers.base[lane] + a.slot_off;
-      bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
-      if ((scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
-      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+    if (row < 0) continue;  // uniform over the warp
+#pragma unroll
+    for (int u = 0; u < kLocalU; ++u) {
+      const int v = (seg * kLocalU + u) * 32 + lane;
+      if ((seg * kLocalU + u) * 32 >= nv32) break;  // uniform over the warp
+      const float s = group_scale(group_amax8(absmax16(raw[u])), kUe8m0);
+      if (v < nv32) {
+        out_x[(size_t)row * nv32 + v] = quant16(raw[u], s);
+        if ((lane & 7) == 0) out_s[(size_t)row * ng + (v >> 3)] = s;
+      }
     }
-    bulk_commit();
-    // metadata: top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
-    long long id = -1;
-    float w = 0.f;
-    if (lane < K) {
-      id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
-                     : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
-      w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
-    }
-    const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
-    for (int d = 0; d < W; ++d) {
-      if (!((dmask >> d) & 1u)) continue;
-      const int row = __shfl_sync(0xffffffffu, my_row, d);
-      char* dst = a.peers.base[d] + a.slot_off;
+    if (seg == 0) {
       if (lane < K) {
-        const bool mine = owner == d;
-        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
-        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
+        const long long id = load_topk_id(a.ids, a.ids_i64, (size_t)t * K + lane);
+        const bool mine = id >= 0 && id < a.e_local;
+        reinterpret_cast<long long*>(base + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id : -1;
+        reinterpret_cast<float*>(base + a.plan.off_w)[(size_t)row * K + lane] = (mine && a.weights) ? a.weights[(size_t)t * K + lane] : 0.f;
       }
-      if (scale_bytes & 15) {  // scale vector not a 16-byte multiple: plain stores
-        float* dsts = reinterpret_cast<float*>(dst + a.plan.off_scales + (size_t)row * scale_bytes);
-        for (int g = lane; g < scale_bytes / 4; g += 32) dsts[g] = s_scale[g];
-      }
+      if (lane == 0) reinterpret_cast<int32_t*>(base + a.plan.off_src)[row] = t;
     }
   }
-  bulk_wait_all();
-  if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
-}
-
-// ---- staged dispatch (W >= 3): quantise once, then push destination by destination.
-// With the direct kernel every rank fans each token out to a random subset of ranks; at W = 8
-// the fabric then behaves like an input-queued switch with head-of-line blocking (measured 54 %
-// of the peer-copy peak against 86 % for the permutation-ordered combine push).  The staged form
-// keeps the single quantisation pass but orders the NVLink traffic: rank r sends to r+1, r+2, ...
-// in interleaved rotation, so at any moment the ranks push along a permutation.
-
-// Phase 1: quantise (or copy) every token that leaves this rank into the local q-stage
-// [t][row | scales] and record send_list[d][p] = t.  Purely local: no flags, no system fence.
-template <int KIND>
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_stage_kernel(const __grid_constant__ HtDispatchArgs a) {
-  extern __shared__ __align__(128) char s_mem[];
-  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
-  const int lane = tid & 31, twarp = ttid >> 5;
-  const int W = a.W, H = a.plan.H;
-  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes, qrow = a.plan.qrow_bytes;
-  const int stage_bytes = (qrow + 127) / 128 * 128;
-  char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
-  const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
-  const int nvec = in_row_bytes / 16;
-  char* my_slot = a.peers.base[a.me] + a.slot_off;
-  int32_t* send_list = reinterpret_cast<int32_t*>(my_slot + a.plan.off_sendlist);
-  int n = 0;
-
-  for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
-    int my_in = 0;
-    if (lane < W) my_in = a.in_rank[(size_t)t * W + lane];
-    const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
-    if (dmask == 0) continue;  // uniform over the team
-    if (twarp == 1 && my_in) send_list[(size_t)lane * a.plan.t_cap + a.send_off[(size_t)t * W + lane]] = t;
-
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
-    int4 raw[kVpt];
-    load_pass(src, nvec, 0, ttid, raw);
-    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
-    float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
-    ++n;
-    if (ttid == 0) {
-      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
-    }
-    team_bar(team);
-    store_pass<KIND>(raw, nvec, 0, ttid, s_row, s_scale, a.ue8m0 != 0);
-    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
-      load_pass(src, nvec, v0, ttid, raw);
-      store_pass<KIND>(raw, nvec, v0, ttid, s_row, s_scale, a.ue8m0 != 0);
-    }
-    if (KIND == B200EP_X_FP8) {
-      const int ng = H / kGroup;
-      for (int g = ttid; g < ng; g += kTeamThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
-    }
-    if (scale_bytes && ttid < (qrow - row_bytes - scale_bytes) / 4) s_scale[scale_bytes / 4 + ttid] = 0.f;  // pad
-    fence_proxy_async_smem();
-    team_bar(team);
-    if (ttid == 0) {
-      bulk_s2g(my_slot + a.plan.off_qstage + (size_t)t * qrow, s_row, qrow);
-      bulk_commit();
-    }
-  }
-  if (ttid == 0) bulk_wait_all();
-}
-
-// Phase 2: push.  Items interleave the W destinations starting at rank me+1 (self last).
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_dispatch_push_kernel(const __grid_constant__ HtDispatchArgs a) {
-  extern __shared__ __align__(128) char s_mem[];
-  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
-  const int lane = tid & 31, twarp = ttid >> 5;
-  const int W = a.W, K = a.plan.K;
-  const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes, qrow = a.plan.qrow_bytes;
-  const int stage_bytes = (qrow + 127) / 128 * 128;
-  char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
-  const int nvec = qrow / 16;
-  const char* my_slot = a.peers.base[a.me] + a.slot_off;
-  const int32_t* send_list = reinterpret_cast<const int32_t*>(my_slot + a.plan.off_sendlist);
-  const char* qstage = my_slot + a.plan.off_qstage;
-  int n = 0;
-  int maxlen = 0;
-  for (int d = 0; d < W; ++d) maxlen = max(maxlen, a.meta->send_count[d]);
-  const long long items = (long long)maxlen * W;
-
-  for (long long i = (long long)blockIdx.x * kTeams + team; i < items; i += (long long)gridDim.x * kTeams) {
-    const int d = (a.me + 1 + (int)(i % W)) % W;
-    const int v = (int)(i / W);
-    if (v >= a.meta->send_count[d]) continue;  // uniform over the team
-    const int t = send_list[(size_t)d * a.plan.t_cap + v];
-    const int row = a.meta->send_base[d] + v;
-    const int4* src = reinterpret_cast<const int4*>(qstage + (size_t)t * qrow);
-    int4 raw[kVpt];
-#pragma unroll
-    for (int u = 0; u < kVpt; ++u) {
-      const int vv = u * kTeamThreads + ttid;
-      if (vv < nvec) raw[u] = ld_cg_v4(src + vv);  // written by the previous kernel: read through L2
-    }
-    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
-    ++n;
-    if (ttid == 0) {
-      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
-    }
-    team_bar(team);
-#pragma unroll
-    for (int u = 0; u < kVpt; ++u) {
-      const int vv = u * kTeamThreads + ttid;
-      if (vv < nvec) reinterpret_cast<int4*>(s_row)[vv] = raw[u];
-    }
-    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
-      for (int vv = v0 + ttid; vv < min(nvec, v0 + kTeamThreads * kVpt); vv += kTeamThreads)
-        reinterpret_cast<int4*>(s_row)[vv] = ld_cg_v4(src + vv);
-    }
-    fence_proxy_async_smem();
-    team_bar(team);
-    char* dst = a.peers.base[d] + a.slot_off;
-    if (ttid == 0) {
-      bulk_s2g(dst + a.plan.off_x + (size_t)row * row_bytes, s_row, row_bytes);
-      if (scale_bytes && (scale_bytes & 15) == 0)
-        bulk_s2g(dst + a.plan.off_scales + (size_t)row * scale_bytes, s_row + row_bytes, scale_bytes);
-      bulk_commit();
-      *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)row * 4) = t;
-    } else if (twarp == 1) {
-      if (lane < K) {
-        const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
-                                       : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
-        const float w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
-        const bool mine = id >= 0 && (int)(id / a.e_local) == d;
-        reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id - (long long)d * a.e_local : -1;
-        reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
-      }
-    } else if (twarp == 2 && scale_bytes && (scale_bytes & 15)) {
-      float* dsts = reinterpret_cast<float*>(dst + a.plan.off_scales + (size_t)row * scale_bytes);
-      const float* ss = reinterpret_cast<const float*>(s_row + row_bytes);
-      for (int g = lane; g < scale_bytes / 4; g += 32) dsts[g] = ss[g];
-    }
-  }
-  if (ttid == 0) bulk_wait_all();
-  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);
 }
 
 __global__ void wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
@@ -545,61 +360,134 @@ struct HtCombineArgs {
   size_t slot_off;
   unsigned long long* epoch_ptr;
   unsigned* chunk_done;  // [kCombChunks] private counters of the overlapped kernel
-  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished, [+1] = role tickets
-  unsigned long long epoch_value;  // overlapped kernel only: the epoch this call publishes (host mirror; HT is never graph-captured)
-  int T, W, me, slot, nstage;
+  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished
+  int T, W, me, slot;
+  int rows_per_piece;    // rows one DMA piece moves (<= stage size)
+  unsigned stage_bytes;  // bytes of one DMA stage
 };
 
-// Expert rank: result row m goes back to (source rank, source token) = stage[t][me] on that rank.
-// Rows whose source is this rank stay where they are; the reduce reads dev_y directly.
-// Same team structure as the dispatch: loads of the next row overlap the bulk copy of this one.
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 2) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
-  extern __shared__ __align__(128) char s_mem[];
-  const int tid = threadIdx.x, team = tid / kTeamThreads, ttid = tid % kTeamThreads;
-  const int W = a.W;
-  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  char* s_team = s_mem + (size_t)team * a.nstage * row_bytes;
-  int n = 0;
-  const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
-  // Work order: consecutive items go to DIFFERENT source ranks, starting at rank me+1, so that at
-  // any moment the W ranks push along a permutation instead of all converging on rank 0 (incast).
-  int maxlen = 0;
-  for (int k = 1; k < W; ++k) {
-    const int s = (a.me + k) % W;
-    maxlen = max(maxlen, a.meta->rank_prefix[s + 1] - a.meta->rank_prefix[s]);
-  }
-  const long long items = (long long)maxlen * (W - 1);
+// Stage on the SOURCE rank: stage[dst rank d][p] = the row rank d returns for the p-th token this
+// rank sent to d (p = send_off[t][d]).  Rank d holds those rows contiguously, in the same order, as
+// rows [rank_prefix[s], rank_prefix[s+1]) of its receive order -- so the push is a block copy.
+__device__ __forceinline__ size_t stage_row_off(const HtPlan& p, int d, int pos, int row_bytes) {
+  return p.off_stage + ((size_t)d * p.t_cap + pos) * row_bytes;
+}
 
-  for (long long i = (long long)blockIdx.x * kTeams + team; i < items; i += (long long)gridDim.x * kTeams) {
-    const int s = (a.me + 1 + (int)(i % (W - 1))) % W;
-    const int v = (int)(i / (W - 1));
-    const int lo = a.meta->rank_prefix[s];
-    if (v >= a.meta->rank_prefix[s + 1] - lo) continue;  // uniform over the team
-    const int m = lo + v;
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
-    int4 raw[kVpt];
-    load_pass(src, nvec, 0, ttid, raw);
-    char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * row_bytes;
-    ++n;
-    if (ttid == 0) {
-      if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
+// ---- software DMA: one thread moves pieces global -> shared -> peer global with TMA bulk copies.
+// kDmaStages stages; loads run kDmaAhead pieces ahead of stores; a stage is loaded again only after the
+// store that last used it has finished READING it (cp.async.bulk.wait_group.read): when load g is issued
+// at least g - kDmaAhead stores are committed, so "at most kDmaStages - kDmaAhead - 1 pending" covers store g - kDmaStages.
+constexpr int kDmaStages = 4;
+constexpr int kDmaAhead = 2;
+struct DmaPipe {
+  char* stage;
+  uint64_t* bar;
+  unsigned stage_bytes;
+  int loads, stores;
+  char* dst[kDmaStages];
+  unsigned bytes[kDmaStages];
+};
+__device__ __forceinline__ void dma_load(DmaPipe& p, const void* src, char* dst, unsigned bytes) {
+  const int g = p.loads++, st = g % kDmaStages;
+  if (g >= kDmaStages) bulk_wait_read<kDmaStages - kDmaAhead - 1>();
+  p.dst[st] = dst;
+  p.bytes[st] = bytes;
+  mbar_expect_tx(&p.bar[st], bytes);
+  bulk_g2s(p.stage + (size_t)st * p.stage_bytes, src, bytes, &p.bar[st]);
+}
+__device__ __forceinline__ void dma_store(DmaPipe& p) {
+  const int g = p.stores++, st = g % kDmaStages;
+  mbar_wait(&p.bar[st], (unsigned)(g / kDmaStages) & 1u);
+  bulk_s2g(p.dst[st], p.stage + (size_t)st * p.stage_bytes, p.bytes[st]);
+  bulk_commit();
+}
+
+// Row ranges of chunk c (source tokens [c*512, (c+1)*512), the last chunk takes the rest) inside every
+// remote source's block of this rank's receive order: s_lo[k][c] for source (me+1+k) % W.
+__device__ __forceinline__ void combine_chunk_bounds(const HtCombineArgs& a, const int32_t* src_idx,
+                                                     int (*s_lo)[kCombChunks + 1]) {
+  const int W = a.W, tid = threadIdx.x;
+  if (tid < (W - 1) * (kCombChunks + 1)) {
+    const int k = tid / (kCombChunks + 1), c = tid % (kCombChunks + 1);
+    const int s = (a.me + 1 + k) % W;
+    int lo = a.meta->rank_prefix[s], hi = a.meta->rank_prefix[s + 1];
+    if (c == kCombChunks) {
+      lo = hi;
+    } else {
+      const int want = c * kCombChunkTokens;
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldcg(src_idx + mid) < want) lo = mid + 1; else hi = mid;
+      }
     }
-    team_bar(team);
-    store_pass<B200EP_X_BF16>(raw, nvec, 0, ttid, s_row, nullptr, false);
-    for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
-      load_pass(src, nvec, v0, ttid, raw);
-      store_pass<B200EP_X_BF16>(raw, nvec, v0, ttid, s_row, nullptr, false);
+    s_lo[k][c] = lo;
+  }
+}
+
+// The driver thread's part of chunk c for CTA `cta` of `nctas`: pieces interleave the remote sources
+// starting at rank me+1, so that at any moment the W ranks push along a permutation (all ranks
+// converging on rank 0 first was measured 2.2x slower).  Returns the number of pieces stored.
+__device__ __forceinline__ int combine_push_chunk(const HtCombineArgs& a, DmaPipe& p, int (*s_lo)[kCombChunks + 1], int c,
+                                                  int cta, int nctas) {
+  const int W = a.W, R = a.rows_per_piece, row_bytes = 2 * a.plan.H;
+  int maxp = 0;
+  for (int k = 0; k < W - 1; ++k) maxp = max(maxp, (s_lo[k][c + 1] - s_lo[k][c] + R - 1) / R);
+  const long long total = (long long)maxp * (W - 1);
+  long long i = cta;
+  int loaded = 0, stored = 0;
+  bool more = true;
+  for (;;) {
+    if (more && loaded - stored < kDmaAhead) {
+      // next valid piece of this CTA
+      bool found = false;
+      while (i < total) {
+        const int k = (int)(i % (W - 1)), j = (int)(i / (W - 1));
+        i += nctas;
+        const int lo = s_lo[k][c] + j * R, hi = min(s_lo[k][c + 1], lo + R);
+        if (lo >= hi) continue;
+        const int s = (a.me + 1 + k) % W;
+        const char* src = reinterpret_cast<const char*>(a.y) + (size_t)lo * row_bytes;
+        char* dst = a.peers.base[s] + a.slot_off + stage_row_off(a.plan, a.me, lo - a.meta->rank_prefix[s], row_bytes);
+        dma_load(p, src, dst, (unsigned)(hi - lo) * (unsigned)row_bytes);
+        ++loaded;
+        found = true;
+        break;
+      }
+      if (found) continue;
+      more = false;
     }
-    fence_proxy_async_smem();
-    team_bar(team);
-    if (ttid == 0) {
-      const int t = __ldcg(src_idx + m);
-      bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_row, row_bytes);
-      bulk_commit();
+    if (stored < loaded) {
+      dma_store(p);
+      ++stored;
+    } else if (!more) {
+      break;
     }
   }
-  if (ttid == 0) bulk_wait_all();
-  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtComb, a.slot, a.me);
+  return stored;
+}
+
+// Phase SEND on its own (phase-by-phase callers): push everything, then signal once.
+__global__ void __launch_bounds__(128, 1) ht_combine_send_kernel(const __grid_constant__ HtCombineArgs a) {
+  extern __shared__ __align__(128) char s_mem[];
+  __shared__ int s_lo[kMaxRanks][kCombChunks + 1];
+  __shared__ __align__(8) uint64_t s_bar[kDmaStages];
+  const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  combine_chunk_bounds(a, src_idx, s_lo);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kDmaStages; ++i) mbar_init(&s_bar[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    DmaPipe p;
+    p.stage = s_mem;
+    p.bar = s_bar;
+    p.stage_bytes = a.stage_bytes;
+    p.loads = p.stores = 0;
+    for (int c = 0; c < kCombChunks; ++c) combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x);
+    bulk_wait_all();
+  }
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, a.W, kFlagHtComb, a.slot, a.me);
 }
 
 __device__ __forceinline__ void acc8(float (&acc)[8], const int4& v) {
@@ -618,308 +506,235 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
   return make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]);
 }
 
-// Source rank: out[t] = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ).
-// One warp per (token, half row); the row pointers are resolved once per item, then the warp walks
-// the half row in batches of 4 vectors per lane with the loads of up to four source rows in flight
-// together (16 x 16 B per lane).  Accumulation order stays d = 0..W-1.
+// out[t][vbeg..vend) = bf16( sum_{d in ranks(t), ascending} fp32(row_d) ): one warp; the row pointers are
+// resolved once, then the warp walks the range in batches of kRedVec vectors per lane with the loads
+// of up to four source rows in flight together.  kMaxSrc = ranks the code is built for.
 constexpr int kRedVec = 4;
-// kMaxSrc = ranks the kernel is built for: the 1- and 2-rank builds hold at most 2 x 4 vectors of source
-// data, fit 64 registers and run 4 CTAs per SM (ncu on the generic build at EP=1: 128 registers,
-// 16 warps per SM, issue slots 35 % busy).
 template <int kMaxSrc>
-__global__ void __launch_bounds__(256, kMaxSrc == 1 ? 4 : (kMaxSrc == 2 ? 3 : 2)) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
+__device__ __forceinline__ void reduce_item(const HtCombineArgs& a, const char* stage, int my_first, int t, int vbeg,
+                                            int vend, int lane) {
   constexpr int kGrp = kMaxSrc < 4 ? kMaxSrc : 4;
+  const int W = a.W, row_bytes = 2 * a.plan.H;
+  const char* rowp = nullptr;
+  if (lane < W && a.in_rank[(size_t)t * W + lane]) {
+    const int pos = a.send_off[(size_t)t * W + lane];
+    rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + pos) * row_bytes
+                        : stage + ((size_t)lane * a.plan.t_cap + pos) * row_bytes;
+  }
+  const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
+  const char* rows[kMaxSrc];
+#pragma unroll
+  for (int d = 0; d < kMaxSrc; ++d)
+    rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
+  int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
+  for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
+    float acc[kRedVec][8];
+#pragma unroll
+    for (int j = 0; j < kRedVec; ++j)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+#pragma unroll
+    for (int d0 = 0; d0 < kMaxSrc; d0 += kGrp) {
+      if ((dmask >> d0) == 0) break;
+      int4 raw[kGrp][kRedVec];
+#pragma unroll
+      for (int dd = 0; dd < kGrp; ++dd) {
+        if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+          for (int j = 0; j < kRedVec; ++j) {
+            const int v = v0 + j * 32 + lane;
+            if (v < vend) raw[dd][j] = ld_cg_v4(rows[d0 + dd] + (size_t)v * 16);
+          }
+        }
+      }
+#pragma unroll
+      for (int dd = 0; dd < kGrp; ++dd) {
+        if ((dmask >> (d0 + dd)) & 1u) {
+#pragma unroll
+          for (int j = 0; j < kRedVec; ++j) {
+            const int v = v0 + j * 32 + lane;
+            if (v < vend) acc8(acc[j], raw[dd][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kRedVec; ++j) {
+      const int v = v0 + j * 32 + lane;
+      if (v < vend) st_na_v4(dst + v, pack8_bf16(acc[j]));
+    }
+  }
+}
+
+// Phase RECV on its own: wait for every peer's push, then reduce (static partition of the items).
+template <int kMaxSrc>
+__global__ void __launch_bounds__(256, kMaxSrc == 2 ? 3 : 2) ht_combine_recv_kernel(const __grid_constant__ HtCombineArgs a) {
   if (a.W > 1) cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagHtComb, a.slot, a.me, a.epoch_ptr);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  const int W = a.W;
-  const int row_bytes = 2 * a.plan.H;
-  const int nvec = row_bytes / 16;
+  const int nvec = 2 * a.plan.H / 16;
   const int nsplit = nvec >= 256 ? 2 : 1;
   const int per = (nvec / nsplit + 31) / 32 * 32;  // vectors per item, multiple of 32
   const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
   const int my_first = a.meta->rank_prefix[a.me];
   const long long items = (long long)a.T * nsplit;
-
   for (long long it = (long long)blockIdx.x * nwarp + warp; it < items; it += (long long)gridDim.x * nwarp) {
     const int t = (int)(it / nsplit), vbeg = (int)(it % nsplit) * per;
-    const int vend = min(nvec, vbeg + per);
-    const char* rowp = nullptr;
-    if (lane < W && a.in_rank[(size_t)t * W + lane]) {
-      rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + a.send_off[(size_t)t * W + lane]) * row_bytes
-                          : stage + ((size_t)t * W + lane) * row_bytes;
+    reduce_item<kMaxSrc>(a, stage, my_first, t, vbeg, min(nvec, vbeg + per), lane);
+  }
+}
+
+// world == 1: the combine is a gather of this rank's own result rows, out[t] = bf16(0 + y[row(t)]) (the
+// fp32 accumulate with a single term), zeros for tokens that were sent nowhere.  Same item shape as
+// the local dispatch: (row, segment of 4 x 1 KB), 32-byte loads and stores, four in flight per lane.
+__global__ void __launch_bounds__(256, 4) ht_combine_local_kernel(const __grid_constant__ HtCombineArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int H = a.plan.H, nv32 = H / 16;
+  const int nseg = (nv32 + 32 * kLocalU - 1) / (32 * kLocalU);
+  const long long items = (long long)a.T * nseg;
+  for (long long it = (long long)blockIdx.x * 8 + warp; it < items; it += (long long)gridDim.x * 8) {
+    const int t = (int)(it / nseg), seg = (int)(it % nseg);
+    const int row = __ldg(a.send_off + t);
+    const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.y) + (size_t)(row < 0 ? 0 : row) * H);
+    V8* dst = reinterpret_cast<V8*>(reinterpret_cast<__nv_bfloat16*>(a.out) + (size_t)t * H);
+    V8 raw[kLocalU];
+#pragma unroll
+    for (int u = 0; u < kLocalU; ++u) {
+      const int v = (seg * kLocalU + u) * 32 + lane;
+      if (row >= 0 && v < nv32) raw[u] = ld_nc_v8(src + v);
+      else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
+      }
     }
-    const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-    const char* rows[kMaxSrc];
 #pragma unroll
-    for (int d = 0; d < kMaxSrc; ++d)
-      rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
-    int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
-    for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
-      float acc[kRedVec][8];
+    for (int u = 0; u < kLocalU; ++u) {
+      const int v = (seg * kLocalU + u) * 32 + lane;
+      if (v >= nv32) continue;
+      V8 o;
 #pragma unroll
-      for (int j = 0; j < kRedVec; ++j)
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
-#pragma unroll
-      for (int d0 = 0; d0 < kMaxSrc; d0 += kGrp) {
-        if ((dmask >> d0) == 0) break;
-        int4 raw[kGrp][kRedVec];
-#pragma unroll
-        for (int dd = 0; dd < kGrp; ++dd) {
-          if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-            for (int j = 0; j < kRedVec; ++j) {
-              const int v = v0 + j * 32 + lane;
-              if (v < vend) raw[dd][j] = ld_cg_v4(rows[d0 + dd] + (size_t)v * 16);
-            }
-          }
-        }
-#pragma unroll
-        for (int dd = 0; dd < kGrp; ++dd) {
-          if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-            for (int j = 0; j < kRedVec; ++j) {
-              const int v = v0 + j * 32 + lane;
-              if (v < vend) acc8(acc[j], raw[dd][j]);
-            }
-          }
-        }
+      for (int i = 0; i < 8; ++i) {
+        const float lo = __fadd_rn(0.f, __uint_as_float(raw[u].w[i] << 16));
+        const float hi = __fadd_rn(0.f, __uint_as_float(raw[u].w[i] & 0xffff0000u));
+        __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+        o.w[i] = *reinterpret_cast<uint32_t*>(&p);
       }
-#pragma unroll
-      for (int j = 0; j < kRedVec; ++j) {
-        const int v = v0 + j * 32 + lane;
-        if (v < vend) st_na_v4(dst + v, pack8_bf16(acc[j]));
-      }
+      asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst + v), "r"(o.w[0]),
+                   "r"(o.w[1]), "r"(o.w[2]), "r"(o.w[3]), "r"(o.w[4]), "r"(o.w[5]), "r"(o.w[6]), "r"(o.w[7])
+                   : "memory");
     }
   }
 }
 
-// ---- overlapped combine (production path, phases == ALL, W > 1).
-// One launch, one CTA per SM, CTAs alternate between two roles:
-//   even CTAs  push result rows back (as ht_combine_send_kernel) but chunk by chunk of 512 source
-//              tokens; after draining a chunk every push CTA arrives on a per-chunk counter and the
-//              last one raises that chunk's flags on all peers (one system fence per chunk, nobody waits);
-//   odd CTAs   reduce (as ht_combine_recv_kernel) chunk c as soon as every peer's chunk-c flag is up.
-// The fp32 reduction of the early chunks therefore runs under the NVLink transfer of the later
-// ones instead of after it.  Push CTAs never wait, so the kernel cannot deadlock; the separate
-// SEND / RECV kernels remain for phase-by-phase callers (single-GPU emulation, recv hooks).
-__global__ void __launch_bounds__(kTeams* kTeamThreads, 1) ht_combine_fused_kernel(const __grid_constant__ HtCombineArgs a) {
+// ---- overlapped combine (production path, phases == ALL, W > 1): one launch, one CTA per SM.
+//   thread 0 of every CTA drives the DMA push chunk by chunk of 512 source tokens; after chunk c+1 is
+//            issued it waits until chunk c has landed (all but the most recent groups complete),
+//            arrives on chunk c's counter, and the last CTA to arrive raises that chunk's flags on all
+//            peers (one system fence per chunk; the pushing never waits for anybody);
+//   the other warps (and warp 0 once its pushes are out) reduce chunk c as soon as every peer's
+//            chunk-c flag is up; items come from a per-chunk queue.
+// The fp32 reduction of the early chunks runs under the NVLink transfer of the later ones, and every
+// SM keeps pushing for the whole transfer.  Nothing here waits for one of this rank's OWN CTAs, so
+// the kernel completes with any number of resident CTAs (the GPU may be shared under DBO).
+// The call epoch is read from device memory by every warp at entry and advanced by the last warp of
+// the grid to finish, together with the rewind of the queues.
+__global__ void __launch_bounds__(512, 1) ht_combine_fused_kernel(const __grid_constant__ HtCombineArgs a) {
   extern __shared__ __align__(128) char s_mem[];
   __shared__ int s_lo[kMaxRanks][kCombChunks + 1];
-  const int tid = threadIdx.x;
+  __shared__ __align__(8) uint64_t s_bar[kDmaStages];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int W = a.W;
-  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  // CTAs alternate push / reduce-only; push CTAs join the reduction once their rows are out and
-  // reduce items are handed out dynamically.  (Measured at EP=8: 1:1 static 483 us, 3:1 502 us --
-  // with fewer reducers the reduction falls behind the transfer and becomes a tail.)
-  // CTAs alternate push / reduce-only by block parity.  Placement matters: putting all push CTAs on
-  // the low block indices (SMs 0..73, one die) cost 793 -> 1014 us per step at EP=8, handing roles out
-  // by start-order tickets 1168 us.  To stay safe when the GPU is shared with other kernels (DBO) and
-  // not every CTA can be resident, a reduce-only CTA first checks that all push CTAs of this rank are
-  // running; if they are not within ~10 us it EXITS (reduce items come from a queue, so the push CTAs
-  // finish the reduction themselves) instead of holding a slot a push CTA may be waiting for.
-  const int nred = gridDim.x >> 1, nsend = gridDim.x - nred;
-  const int role = blockIdx.x & 1;
-  const int ridx = blockIdx.x >> 1;
-  unsigned* started = &a.red_next[kCombChunks + 1];
-  auto finish = [&]() {  // every warp of the grid, exactly once: the last one rewinds the counters
-    if ((tid & 31) == 0) {
-      const unsigned prev = atomicAdd(&a.red_next[kCombChunks], 1u);
-      if (prev == gridDim.x * (blockDim.x >> 5) - 1)
-        for (int c = 0; c <= kCombChunks + 1; ++c) a.red_next[c] = 0;
-    }
-  };
-  if (role == 0) {
-    if (tid == 0) atomicAdd(started, 1u);
-  } else {
-    __shared__ int s_go;
-    if (tid == 0) {
-      const long long t0 = clock64();
-      while (*reinterpret_cast<volatile unsigned*>(started) < (unsigned)nsend && clock64() - t0 < 20000) {
-      }
-      s_go = *reinterpret_cast<volatile unsigned*>(started) >= (unsigned)nsend;
-    }
-    __syncthreads();
-    if (!s_go) {
-      finish();
-      return;
-    }
-  }
+  const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(a.epoch_ptr) + 1;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  combine_chunk_bounds(a, src_idx, s_lo);
+  if (tid == 0) {
+    for (int i = 0; i < kDmaStages; ++i) mbar_init(&s_bar[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
 
-  if (role == 0) {
-    // ------------------------------------------------ push role
-    const int team = tid / kTeamThreads, ttid = tid % kTeamThreads;
-    char* s_team = s_mem + (size_t)team * a.nstage * row_bytes;
-    int n = 0;
-    // chunk bounds of every remote source's row range: rows are ascending in source token
-    if (tid < (W - 1) * (kCombChunks + 1)) {
-      const int k = tid / (kCombChunks + 1), c = tid % (kCombChunks + 1);
-      const int s = (a.me + 1 + k) % W;
-      int lo = a.meta->rank_prefix[s], hi = a.meta->rank_prefix[s + 1];
-      if (c == kCombChunks) {
-        lo = hi;
-      } else {
-        const int want = c * kCombChunkTokens;
-        while (lo < hi) {
-          const int mid = (lo + hi) >> 1;
-          if (__ldcg(src_idx + mid) < want) lo = mid + 1; else hi = mid;
-        }
-      }
-      s_lo[k][c] = lo;
-    }
-    __syncthreads();
-    // Completion of chunk c is published one chunk late (after chunk c+1 has been issued), so the
-    // wait for the last rows of a chunk to land overlaps the next chunk's transfers.
+  if (tid == 0) {
+    // ------------------------------------------------ push (DMA driver)
+    DmaPipe p;
+    p.stage = s_mem;
+    p.bar = s_bar;
+    p.stage_bytes = a.stage_bytes;
+    p.loads = p.stores = 0;
     auto arrive = [&](int c) {
-      __syncthreads();
-      if (tid == 0) {
-        const unsigned prev = atom_add_acq_rel_gpu(&a.chunk_done[c], 1u);
-        if (prev == (unsigned)nsend - 1) {
-          a.chunk_done[c] = 0;
-          fence_acq_rel_sys();
-          for (int d = 0; d < W; ++d)
-            if (d != a.me)
-              st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), a.epoch_value);
-          if (c == kCombChunks - 1) *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = a.epoch_value;
-        }
+      const unsigned prev = atom_add_acq_rel_gpu(&a.chunk_done[c], 1u);
+      if (prev == gridDim.x - 1) {
+        a.chunk_done[c] = 0;
+        fence_acq_rel_sys();
+        for (int d = 0; d < W; ++d)
+          if (d != a.me)
+            st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), want);
       }
     };
     for (int c = 0; c < kCombChunks; ++c) {
-      int issued = 0;  // bulk groups this team's issuing thread committed in chunk c
-      int maxlen = 0;
-      for (int k = 0; k < W - 1; ++k) maxlen = max(maxlen, s_lo[k][c + 1] - s_lo[k][c]);
-      const long long items = (long long)maxlen * (W - 1);
-      for (long long i = (long long)ridx * kTeams + team; i < items; i += (long long)nsend * kTeams) {
-        const int k = (int)(i % (W - 1));
-        const int m = s_lo[k][c] + (int)(i / (W - 1));
-        if (m >= s_lo[k][c + 1]) continue;  // uniform over the team
-        const int s = (a.me + 1 + k) % W;
-        const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)m * row_bytes);
-        int4 raw[kVpt];
-        load_pass(src, nvec, 0, ttid, raw);
-        char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * row_bytes;
-        ++n;
-        if (ttid == 0) {
-          if (a.nstage == 2) bulk_wait_read1(); else bulk_wait_read0();
-        }
-        team_bar(team);
-        store_pass<B200EP_X_BF16>(raw, nvec, 0, ttid, s_row, nullptr, false);
-        for (int v0 = kTeamThreads * kVpt; v0 < nvec; v0 += kTeamThreads * kVpt) {
-          load_pass(src, nvec, v0, ttid, raw);
-          store_pass<B200EP_X_BF16>(raw, nvec, v0, ttid, s_row, nullptr, false);
-        }
-        fence_proxy_async_smem();
-        team_bar(team);
-        if (ttid == 0) {
-          const int t = __ldcg(src_idx + m);
-          bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + ((size_t)t * W + a.me) * row_bytes, s_row, row_bytes);
-          bulk_commit();
-          ++issued;
-        }
-      }
+      const int issued = combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x);
       if (c > 0) {
-        // everything older than this chunk's (>= 4) most recent groups has landed -> chunk c-1 is complete here
-        if (ttid == 0) {
-          if (issued >= 4) asm volatile("cp.async.bulk.wait_group 4;" ::: "memory");
-          else bulk_wait_all();
-        }
+        // everything older than this chunk's most recent groups has landed -> chunk c-1 is complete here
+        if (issued >= 2) bulk_wait<2>(); else bulk_wait_all();
         arrive(c - 1);
       }
     }
-    if (ttid == 0) bulk_wait_all();
+    bulk_wait_all();
     arrive(kCombChunks - 1);
   }
-  {
-    // ------------------------------------------------ reduce (every CTA; push CTAs arrive late)
-    (void)nred;
-    const int lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-    const int nsplit = nvec >= 256 ? 2 : 1;
-    const int per = (nvec / nsplit + 31) / 32 * 32;
-    const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
-    const int my_first = a.meta->rank_prefix[a.me];
-    for (int c = 0; c < kCombChunks; ++c) {
-      const int t0 = c * kCombChunkTokens;
-      const int t1 = c == kCombChunks - 1 ? a.T : min(a.T, t0 + kCombChunkTokens);
-      if (tid < W && tid != a.me)
-        wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagHtCombChunk0 + c, a.slot, tid)),
-                      a.epoch_value, kFlagHtCombChunk0 + c, a.me, tid);
-      __syncthreads();
-      if (t1 <= t0) continue;
-      const int items = (t1 - t0) * nsplit;
-      for (;;) {
-        int it = 0;
-        if (lane == 0) it = (int)atomicAdd(&a.red_next[c], 1u);
-        it = __shfl_sync(0xffffffffu, it, 0);
-        if (it >= items) break;
-        const int t = t0 + it / nsplit, vbeg = (it % nsplit) * per;
-        const int vend = min(nvec, vbeg + per);
-        const char* rowp = nullptr;
-        if (lane < W && a.in_rank[(size_t)t * W + lane]) {
-          rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + a.send_off[(size_t)t * W + lane]) * row_bytes
-                              : stage + ((size_t)t * W + lane) * row_bytes;
-        }
-        const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-        const char* rows[kMaxRanks];
-#pragma unroll
-        for (int d = 0; d < kMaxRanks; ++d)
-          rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
-        int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
-        for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
-          float acc[kRedVec][8];
-#pragma unroll
-          for (int j = 0; j < kRedVec; ++j)
-#pragma unroll
-            for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
-#pragma unroll
-          for (int d0 = 0; d0 < kMaxRanks; d0 += 4) {
-            if ((dmask >> d0) == 0) break;
-            int4 raw[4][kRedVec];
-#pragma unroll
-            for (int dd = 0; dd < 4; ++dd) {
-              if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-                for (int j = 0; j < kRedVec; ++j) {
-                  const int v = v0 + j * 32 + lane;
-                  if (v < vend) raw[dd][j] = ld_cg_v4(rows[d0 + dd] + (size_t)v * 16);
-                }
-              }
-            }
-#pragma unroll
-            for (int dd = 0; dd < 4; ++dd) {
-              if ((dmask >> (d0 + dd)) & 1u) {
-#pragma unroll
-                for (int j = 0; j < kRedVec; ++j) {
-                  const int v = v0 + j * 32 + lane;
-                  if (v < vend) acc8(acc[j], raw[dd][j]);
-                }
-              }
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < kRedVec; ++j) {
-            const int v = v0 + j * 32 + lane;
-            if (v < vend) st_na_v4(dst + v, pack8_bf16(acc[j]));
-          }
-        }
-      }
+  __syncwarp();
+
+  // ------------------------------------------------ reduce (every warp; warp 0 arrives late)
+  const int nvec = 2 * a.plan.H / 16;
+  const int nsplit = nvec >= 256 ? 2 : 1;
+  const int per = (nvec / nsplit + 31) / 32 * 32;
+  const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
+  const int my_first = a.meta->rank_prefix[a.me];
+  for (int c = 0; c < kCombChunks; ++c) {
+    const int t0 = c * kCombChunkTokens;
+    const int t1 = c == kCombChunks - 1 ? a.T : min(a.T, t0 + kCombChunkTokens);
+    if (lane < W && lane != a.me)
+      wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagHtCombChunk0 + c, a.slot, lane)), want,
+                    kFlagHtCombChunk0 + c, a.me, lane);
+    __syncwarp();
+    if (t1 <= t0) continue;
+    const int items = (t1 - t0) * nsplit;
+    for (;;) {
+      int it = 0;
+      if (lane == 0) it = (int)atomicAdd(&a.red_next[c], 1u);
+      it = __shfl_sync(0xffffffffu, it, 0);
+      if (it >= items) break;
+      const int t = t0 + it / nsplit, vbeg = (it % nsplit) * per;
+      reduce_item<kMaxRanks>(a, stage, my_first, t, vbeg, min(nvec, vbeg + per), lane);
     }
-    finish();  // the last warp of the whole grid to run out of work rewinds the counters for the next call
+  }
+  // the last warp of the whole grid to run out of work rewinds the queues and advances the epoch
+  // (every warp has read the old epoch by then)
+  if (lane == 0) {
+    const unsigned prev = atom_add_acq_rel_gpu(&a.red_next[kCombChunks], 1u);
+    if (prev == gridDim.x * (blockDim.x >> 5) - 1) {
+      for (int c = 0; c <= kCombChunks; ++c) a.red_next[c] = 0;
+      *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = want;
+    }
   }
 }
 
-static int grid_for(const b200ep_ctx* c, int items, int per_cta, int ctas_per_sm) {
+static int grid_for(const b200ep_ctx* c, long long items, int per_cta, int ctas_per_sm) {
   int sms = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
-  int g = (items + per_cta - 1) / per_cta;
-  int cap = sms * ctas_per_sm;
+  long long g = (items + per_cta - 1) / per_cta;
+  long long cap = (long long)sms * ctas_per_sm;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  return g;
+  return (int)g;
 }
 
 }  // namespace b200ep
 
 using namespace b200ep;
+
+namespace b200ep {
+int launch_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
+                  int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert, uint8_t* dev_is_token_in_rank,
+                  int32_t* dev_send_off, const NotifyTail& tail, cudaStream_t st);
+}
 
 static int check_slot(b200ep_ctx* c, int slot, const char* who) {
   if (!c || slot < 0 || slot >= kNumSlots) {
@@ -977,14 +792,13 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
   return B200EP_OK;
 }
 
-extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
-                                  int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
-                                  const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H, int K,
-                                  int E, int phases, void* stream) {
-  int rc = check_slot(c, slot, "ht_dispatch");
-  if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  B200EP_CUDA(cudaSetDevice(c->device));
+// SEND / RECV launches of the dispatch.  prologue: the kernel itself waits for the peers' counts
+// (production path, b200ep_ht_dispatch_all) instead of relying on an earlier notify-recv launch.
+static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind, int ue8m0,
+                           const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
+                           const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H, int K, int E,
+                           int phases, int prologue, cudaStream_t st) {
+  int rc;
   if (phases & B200EP_PHASE_SEND) {
     HtPlan plan;
     rc = make_ht_plan(c, H, K, x_kind, &plan);
@@ -1007,6 +821,10 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
       set_error("ht_dispatch: null pointer");
       return B200EP_ERR_ARG;
     }
+    if (T > 0 && ((uintptr_t)dev_x & 31)) {
+      set_error("ht_dispatch: x must be 32-byte aligned");
+      return B200EP_ERR_ARG;
+    }
     c->ht_plan[slot] = plan;
     c->ht_tokens[slot] = T;
     HtDispatchArgs a;
@@ -1019,9 +837,11 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.in_rank = dev_is_token_in_rank;
     a.send_off = dev_send_off;
     a.meta = &c->local->ht[slot];
+    a.host = c->host_dev;
     a.done = &c->local->done[0 + slot];
     a.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
     a.epoch_ptr = &c->local->epoch[kFlagHtData][slot];
+    a.notify_epoch_ptr = &c->local->epoch[kFlagHtNotify][slot];
     a.T = T;
     a.W = c->world;
     a.me = c->rank;
@@ -1029,48 +849,62 @@ extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, co
     a.e_local = E / c->world;
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
-    const size_t stage_bytes = (size_t)(plan.qrow_bytes + 127) / 128 * 128;
-    a.nstage = 2 * kTeams * stage_bytes <= 100 * 1024 ? 2 : 1;  // two CTAs per SM must still fit
-    const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
-    const int grid = grid_for(c, T, kTeams, x_kind == B200EP_X_BF16_QUANT ? 3 : 2);
-    auto launch = [&](auto kern, int g) -> int {
-      B200EP_CUDA(ensure_dynamic_smem((const void*)kern, c->device, (int)smem));
-      kern<<<g, kTeams * kTeamThreads, smem, st>>>(a);
+    a.prologue = (prologue && c->world > 1) ? 1 : 0;
+    static const int meta_env = getenv("B200EP_HT_META_BULK") ? atoi(getenv("B200EP_HT_META_BULK")) : 1;
+    a.meta_bulk = (meta_env && K % 4 == 0 && c->world > 1) ? 1 : 0;
+    if (c->world == 1 && x_kind == B200EP_X_BF16_QUANT && H % 16 == 0) {
+      // single rank: registers -> receive region, no staging
+      a.nstage = 0;
+      const int nseg = (H / 16 + 32 * kLocalU - 1) / (32 * kLocalU);
+      const int grid = grid_for(c, (long long)T * nseg, 8, 3);
+      if (H == 7168) {
+        if (ue8m0) ht_dispatch_local_kernel<7168, true><<<grid, 256, 0, st>>>(a);
+        else ht_dispatch_local_kernel<7168, false><<<grid, 256, 0, st>>>(a);
+      } else {
+        if (ue8m0) ht_dispatch_local_kernel<0, true><<<grid, 256, 0, st>>>(a);
+        else ht_dispatch_local_kernel<0, false><<<grid, 256, 0, st>>>(a);
+      }
       B200EP_CUDA(cudaGetLastError());
-      return B200EP_OK;
-    };
-    // Optional (B200EP_HT_STAGED=1): quantise once into the local q-stage, then push in permutation
-    // order.  Measured at EP=8 it is SLOWER than the direct fan-out (326 vs 250 us per dispatch), so
-    // the direct kernel stays the default; the staged form is kept for experiments.
-    static const int staged_env = getenv("B200EP_HT_STAGED") ? atoi(getenv("B200EP_HT_STAGED")) : 0;
-    const bool staged = staged_env != 0 && c->world > 1;
-    // Experiment, off by default: measured 31.0 us at EP=1 against 26.5 us for the team kernel (fewer
-    // instructions, 9.8 M vs 11.9 M, but each warp serialises load -> quantise over 3.5 passes per row).
-    static const int warp_env = getenv("B200EP_HT_WARP_KERNEL") ? atoi(getenv("B200EP_HT_WARP_KERNEL")) : 0;
-    if (!staged && x_kind == B200EP_X_BF16_QUANT && warp_env && kWarpCtaWarps * stage_bytes <= 220 * 1024) {
-      const size_t wsmem = (size_t)kWarpCtaWarps * stage_bytes;
-      B200EP_CUDA(ensure_dynamic_smem((const void*)ht_dispatch_send_warp_kernel, c->device, (int)wsmem));
-      ht_dispatch_send_warp_kernel<<<grid_for(c, T, kWarpCtaWarps, 1), kWarpCtaWarps * 32, wsmem, st>>>(a);
-      B200EP_CUDA(cudaGetLastError());
-    } else if (!staged) {
-      if (x_kind == B200EP_X_BF16_QUANT && H == 7168) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT, 7168>, grid);
-      else if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>, grid);
-      else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>, grid);
-      else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>, grid);
     } else {
-      if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_stage_kernel<B200EP_X_BF16_QUANT>, grid);
-      else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_stage_kernel<B200EP_X_FP8>, grid);
-      else rc = launch(ht_dispatch_stage_kernel<B200EP_X_BF16>, grid);
+      const size_t meta_off = (size_t)(plan.row_bytes + plan.scale_bytes + 15) / 16 * 16;
+      const size_t stage_bytes = (meta_off + (a.meta_bulk ? (size_t)c->world * K * 12 : 0) + 127) / 128 * 128;
+      const int ctas_per_sm = x_kind == B200EP_X_BF16_QUANT ? 3 : 2;
+      a.nstage = 2 * kTeams * stage_bytes * ctas_per_sm <= 216 * 1024 ? 2 : 1;  // every resident CTA must still fit
+      const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
+      if (smem > 220 * 1024) {
+        set_error("ht_dispatch: a row of %d bytes does not fit the shared-memory stage", plan.row_bytes);
+        return B200EP_ERR_ARG;
+      }
+      const int grid = grid_for(c, T, kTeams, ctas_per_sm);
+      auto launch = [&](auto kern) -> int {
+        B200EP_CUDA(ensure_dynamic_smem((const void*)kern, c->device, (int)smem));
+        kern<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
+        B200EP_CUDA(cudaGetLastError());
+        return B200EP_OK;
+      };
+      if (x_kind == B200EP_X_BF16_QUANT && H == 7168) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT, 7168>);
+      else if (x_kind == B200EP_X_BF16_QUANT) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT>);
+      else if (x_kind == B200EP_X_FP8) rc = launch(ht_dispatch_send_kernel<B200EP_X_FP8>);
+      else rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16>);
       if (rc) return rc;
-      rc = launch(ht_dispatch_push_kernel, grid_for(c, T * 6, kTeams, 2));
     }
-    if (rc) return rc;
   }
   if ((phases & B200EP_PHASE_RECV) && c->world > 1) {  // a single rank has nobody to wait for
     wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, &c->local->epoch[kFlagHtData][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
+}
+
+extern "C" int b200ep_ht_dispatch(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
+                                  int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
+                                  const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H, int K,
+                                  int E, int phases, void* stream) {
+  int rc = check_slot(c, slot, "ht_dispatch");
+  if (rc) return rc;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  return dispatch_launch(c, slot, dev_x, dev_x_scales, x_kind, ue8m0, dev_topk_ids, ids_i64, dev_topk_weights,
+                         dev_is_token_in_rank, dev_send_off, T, H, K, E, phases, 0, (cudaStream_t)stream);
 }
 
 extern "C" int b200ep_ht_views(b200ep_ctx* c, int slot, b200ep_ht_view* out) {
@@ -1122,82 +956,112 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.me = c->rank;
   a.slot = slot;
   a.epoch_ptr = &c->local->epoch[kFlagHtComb][slot];
-  const int row_bytes = 2 * H;
   a.chunk_done = &c->local->done[16 + slot * kCombChunks];
   a.red_next = &c->local->done[32 + slot * 16];
-  a.epoch_value = 0;
-  static const int overlap_env = getenv("B200EP_HT_OVERLAP") ? atoi(getenv("B200EP_HT_OVERLAP")) : 1;
-  if (phases == B200EP_PHASE_ALL && c->world > 1 && overlap_env) {
-    // production path: push and reduce overlapped in one launch (see ht_combine_fused_kernel)
-    if (T > 0 && (!dev_out || !dev_is_token_in_rank || !dev_send_off)) {
-      set_error("ht_combine: null pointer");
+  const int row_bytes = 2 * H;
+  // DMA pieces: as many whole rows as fit 44 KB (4 stages of it stay within one SM's shared memory)
+  a.rows_per_piece = 44 * 1024 / row_bytes;
+  if (a.rows_per_piece < 1) a.rows_per_piece = 1;
+  static const int piece_env = getenv("B200EP_HT_PIECE_ROWS") ? atoi(getenv("B200EP_HT_PIECE_ROWS")) : 0;
+  if (piece_env > 0 && piece_env < a.rows_per_piece) a.rows_per_piece = piece_env;
+  a.stage_bytes = (unsigned)a.rows_per_piece * (unsigned)row_bytes;
+  const size_t dma_smem = (size_t)kDmaStages * a.stage_bytes;
+  const bool any = phases & (B200EP_PHASE_SEND | B200EP_PHASE_RECV);
+  if (any && T > 0 && (!dev_out || !dev_is_token_in_rank || !dev_send_off) && (phases & B200EP_PHASE_RECV)) {
+    set_error("ht_combine: null pointer");
+    return B200EP_ERR_ARG;
+  }
+  if (c->world == 1) {  // a single rank pushes nothing: the gather reads dev_y directly
+    if (phases & B200EP_PHASE_RECV) {
+      if (T > 0 && (((uintptr_t)dev_y | (uintptr_t)dev_out) & 31)) {
+        set_error("ht_combine: y and out must be 32-byte aligned");
+        return B200EP_ERR_ARG;
+      }
+      const int nseg = (H / 16 + 32 * kLocalU - 1) / (32 * kLocalU);
+      ht_combine_local_kernel<<<grid_for(c, (long long)T * nseg, 8, 4), 256, 0, st>>>(a);
+      B200EP_CUDA(cudaGetLastError());
+    }
+    return B200EP_OK;
+  }
+  if ((phases & B200EP_PHASE_SEND) && (!dev_y || ((uintptr_t)dev_y & 15))) {
+    // (dev_y may only be null when this rank received nothing; a null pointer is never dereferenced then)
+    if (dev_y || c->ht_tokens[slot] < 0) {
+      set_error("ht_combine: y must be 16-byte aligned");
       return B200EP_ERR_ARG;
     }
-    a.epoch_value = ++c->epoch[kFlagHtComb][slot];
-    a.nstage = 2 * (size_t)kTeams * row_bytes <= 200 * 1024 ? 2 : 1;
-    const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
-    int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
-    if (grid < 4) grid = 4;
-    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_fused_kernel, c->device, (int)smem));
-    ht_combine_fused_kernel<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
+  }
+  if (dma_smem > 200 * 1024) {
+    set_error("ht_combine: a row of %d bytes does not fit the DMA stages", row_bytes);
+    return B200EP_ERR_ARG;
+  }
+  int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
+  static const int overlap_env = getenv("B200EP_HT_OVERLAP") ? atoi(getenv("B200EP_HT_OVERLAP")) : 1;
+  if (phases == B200EP_PHASE_ALL && overlap_env) {
+    // production path: push and reduce overlapped in one launch (see ht_combine_fused_kernel)
+    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_fused_kernel, c->device, (int)dma_smem));
+    ht_combine_fused_kernel<<<grid, 512, dma_smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
     return B200EP_OK;
   }
-  if ((phases & B200EP_PHASE_SEND) && c->world > 1) {  // a single rank pushes nothing: the reduce reads dev_y directly
-    ++c->epoch[kFlagHtComb][slot];  // host mirror of the device epoch (used by the overlapped path)
-    a.nstage = 2 * (size_t)kTeams * row_bytes <= 100 * 1024 ? 2 : 1;
-    int ctas_per_sm = 2;
-    if (a.nstage == 1 && 2 * (size_t)kTeams * row_bytes <= 200 * 1024) {  // wide rows: one CTA per SM, still two stages
-      a.nstage = 2;
-      ctas_per_sm = 1;
-    }
-    // M lives on the device; the host mirror of the last notify gives the grid size
-    const int M = c->host->num_recv_cache[slot];
-    const size_t smem = (size_t)kTeams * a.nstage * row_bytes;
-    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_send_kernel, c->device, (int)smem));
-    ht_combine_send_kernel<<<grid_for(c, M, kTeams, ctas_per_sm), kTeams * kTeamThreads, smem, st>>>(a);
+  if (phases & B200EP_PHASE_SEND) {
+    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_send_kernel, c->device, (int)dma_smem));
+    ht_combine_send_kernel<<<grid, 128, dma_smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_PHASE_RECV) {
-    if (T > 0 && (!dev_out || !dev_is_token_in_rank || !dev_send_off)) {
-      set_error("ht_combine: null pointer");
-      return B200EP_ERR_ARG;
-    }
     const int nsplit = row_bytes / 16 >= 256 ? 2 : 1;
-    if (c->world == 1) ht_combine_recv_kernel<1><<<grid_for(c, T * nsplit, 8, 4), 256, 0, st>>>(a);
-    else if (c->world == 2) ht_combine_recv_kernel<2><<<grid_for(c, T * nsplit, 8, 3), 256, 0, st>>>(a);
-    else ht_combine_recv_kernel<kMaxRanks><<<grid_for(c, T * nsplit, 8, 2), 256, 0, st>>>(a);
+    if (c->world == 2) ht_combine_recv_kernel<2><<<grid_for(c, (long long)T * nsplit, 8, 3), 256, 0, st>>>(a);
+    else ht_combine_recv_kernel<kMaxRanks><<<grid_for(c, (long long)T * nsplit, 8, 2), 256, 0, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
   return B200EP_OK;
 }
 
-
-// One host call for the whole dispatch: layout -> count exchange -> host wait -> payload (+ wait).
-// Same kernels as the separate entry points; exists because at EP=1 the step is bound by the
-// caller's per-call overhead (ctypes crossings), not by the GPU.
+// One host call for the whole dispatch (deep_ep.Buffer.get_dispatch_layout + Buffer.dispatch,
+// deepep_ht.py:121-162): the layout kernel (whose last block publishes the counts), the dispatch kernel
+// (which waits for the peers' counts itself) and the wait for the payload are all queued BEFORE the
+// host waits for the counts, so the host round trip runs under the dispatch kernel instead of in front of it.
 extern "C" int b200ep_ht_dispatch_all(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind,
                                       int ue8m0, const void* dev_topk_ids, int ids_i64, const float* dev_topk_weights,
                                       int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
                                       uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, int T, int H, int K, int E,
                                       int* num_recv_tokens, int32_t* per_expert, int32_t* rank_prefix, int timeout_ms,
                                       void* stream) {
-  int rc = b200ep_layout(c, dev_topk_ids, ids_i64, T, K, E, dev_tokens_per_rank, dev_tokens_per_expert,
-                         dev_is_token_in_rank, dev_send_off, stream);
+  int rc = check_slot(c, slot, "ht_dispatch_all");
   if (rc) return rc;
-  rc = b200ep_ht_notify(c, slot, dev_tokens_per_rank, dev_tokens_per_expert, E, B200EP_PHASE_ALL, stream);
-  if (rc) return rc;
-  if (timeout_ms >= 0) {
-    rc = b200ep_ht_notify_wait(c, slot, num_recv_tokens, per_expert, rank_prefix, timeout_ms);
-    if (rc) return rc;
-  } else {
-    // host-sync-free mode: the caller sized its views for a worst case; counts stay on the device
-    // (b200ep_ht_views: rank_prefix[world] = rows received, recv_per_expert).  Later grids assume the worst.
+  if (E <= 0 || E % c->world || E / c->world > kMaxLocalExperts) {
+    set_error("ht_dispatch_all: bad E=%d for world=%d", E, c->world);
+    return B200EP_ERR_ARG;
+  }
+  {  // validate the shape before anything is queued: a failure after the counts are out would leave the peers waiting
     HtPlan plan;
     rc = make_ht_plan(c, H, K, x_kind, &plan);
     if (rc) return rc;
-    c->host->num_recv_cache[slot] = plan.cap_rows;
+    if (T < 0 || T > plan.t_cap) {
+      set_error("ht_dispatch: T=%d exceeds slot capacity %d tokens/rank (H=%d K=%d kind=%d, region %zu bytes)", T,
+                plan.t_cap, H, K, x_kind, c->sym_bytes);
+      return B200EP_ERR_CAPACITY;
+    }
   }
-  return b200ep_ht_dispatch(c, slot, dev_x, dev_x_scales, x_kind, ue8m0, dev_topk_ids, ids_i64, dev_topk_weights,
-                            dev_is_token_in_rank, dev_send_off, T, H, K, E, B200EP_PHASE_ALL, stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  NotifyTail tail;
+  tail.peers = c->peers;
+  tail.meta = &c->local->ht[slot];
+  tail.host = c->host_dev;
+  tail.epoch_ptr = &c->local->epoch[kFlagHtNotify][slot];
+  tail.mode = c->world == 1 ? kTailLocal : kTailPublish;
+  tail.me = c->rank;
+  tail.slot = slot;
+  ++c->epoch[kFlagHtNotify][slot];  // host mirror of the device epoch, for b200ep_ht_notify_wait
+  c->ht_e_local[slot] = E / c->world;
+  rc = launch_layout(c, dev_topk_ids, ids_i64, T, K, E, dev_tokens_per_rank, dev_tokens_per_expert, dev_is_token_in_rank,
+                     dev_send_off, tail, st);
+  if (rc) return rc;
+  rc = dispatch_launch(c, slot, dev_x, dev_x_scales, x_kind, ue8m0, dev_topk_ids, ids_i64, dev_topk_weights,
+                       dev_is_token_in_rank, dev_send_off, T, H, K, E, B200EP_PHASE_ALL, 1, st);
+  if (rc) return rc;
+  if (timeout_ms >= 0) return b200ep_ht_notify_wait(c, slot, num_recv_tokens, per_expert, rank_prefix, timeout_ms);
+  // host-sync-free mode: the caller sized its views for a worst case; counts stay on the device
+  // (b200ep_ht_views: rank_prefix[world] = rows received, recv_per_expert)
+  return B200EP_OK;
 }

@@ -13,26 +13,52 @@
 //     block b sums the totals of blocks < b (all resident; a ticket makes the
 //     logical block id follow scheduling order, so the wait cannot deadlock);
 //   * expert histogram in shared memory, flushed with integer atomics (counts
-//     only -- the result does not depend on arrival order).
+//     only -- the result does not depend on arrival order) into private scratch;
+//     the last block to finish writes the totals out, rewinds the scratch and,
+//     on the production path, publishes the counts to the peers (notify.cuh).
 // HBM traffic: T*K ids in, T*W*(1+4) bytes out; latency bound at prefill sizes.
-#include "common.cuh"
+#include "notify.cuh"
 
 namespace b200ep {
 
+// Spin on a published (tag << 32 | count) word until its tag matches; traps instead of hanging.
+__device__ __forceinline__ uint64_t layout_wait_pub(const unsigned long long* p, unsigned tag) {
+  uint64_t v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(p));
+  if ((unsigned)(v >> 32) == tag) return v;
+  const long long t0 = clock64();
+  do {
+    if (clock64() - t0 > 20000000000LL) {  // ~10 s: the publishing block always runs (see ticket), so this is a bug or a dead GPU
+      printf("b200ep: routing layout block %d timed out waiting for an earlier block's totals (tag %u, have %llu)\n",
+             (int)blockIdx.x, tag, (unsigned long long)v);
+      __trap();
+    }
+    v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(p));
+  } while ((unsigned)(v >> 32) != tag);
+  return v;
+}
+
+// All per-call state (block ticket, finished-block count, call epoch, expert histogram) lives in the
+// context's private device scratch and is rewound by the last block to finish: nothing is passed in
+// from host counters and nothing is cleared by a memset, so the launch can be replayed.  Calls on ONE
+// context must not overlap on the GPU (they share that scratch): issue them on one stream.
+// The last block also opens the count exchange of the dispatch that follows (tail.mode, notify.cuh).
 template <typename IdT, bool kSingleTile>
 __global__ void __launch_bounds__(256)
     layout_kernel(const IdT* __restrict__ ids, int T, int K, int E, int W, int e_local,
                   int32_t* __restrict__ tok_per_rank, int32_t* __restrict__ tok_per_expert,
                   uint8_t* __restrict__ in_rank, int32_t* __restrict__ send_off, LocalScratch* ls,
-                  unsigned long long ticket_base, unsigned epoch, int tiles_per_block) {
+                  int tiles_per_block, const __grid_constant__ NotifyTail tail) {
   extern __shared__ int s_hist[];  // [E]
   __shared__ int s_warp_tot[8][kMaxRanks];
   __shared__ int s_tile_base[kMaxRanks];
   __shared__ int s_base[kMaxRanks];
-  __shared__ unsigned s_bid;
+  __shared__ unsigned s_bid, s_tag, s_last;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_bid = (unsigned)(atomicAdd(&ls->layout_ticket, 1ull) - ticket_base);
+  if (tid == 0) {
+    s_tag = (unsigned)(*reinterpret_cast<volatile unsigned long long*>(&ls->layout_epoch) + 1);
+    s_bid = (unsigned)atomicAdd(&ls->layout_ticket, 1ull);  // logical block id follows scheduling order: look-back cannot deadlock
+  }
   for (int e = tid; e < E; e += 256) s_hist[e] = 0;
   if (tid < kMaxRanks) {
     s_tile_base[tid] = 0;
@@ -40,6 +66,7 @@ __global__ void __launch_bounds__(256)
   }
   __syncthreads();
   const int bid = (int)s_bid;
+  const unsigned tag = s_tag;
 
   int loc[kMaxRanks];       // single-tile path: block-local offsets kept in registers
   unsigned my_mask = 0;
@@ -97,21 +124,14 @@ __global__ void __launch_bounds__(256)
   // publish this block's totals, then sum the totals of all logically earlier blocks
   if (tid < W)
     st_release_gpu_u64(reinterpret_cast<uint64_t*>(&ls->layout_pub[bid][tid]),
-                       ((uint64_t)epoch << 32) | (uint32_t)s_tile_base[tid]);
+                       ((uint64_t)tag << 32) | (uint32_t)s_tile_base[tid]);
   int part[kMaxRanks];
 #pragma unroll
   for (int d = 0; d < kMaxRanks; ++d) part[d] = 0;
   for (int b = tid; b < bid; b += 256) {
 #pragma unroll
-    for (int d = 0; d < kMaxRanks; ++d) {
-      if (d < W) {
-        uint64_t v;
-        do {
-          v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(&ls->layout_pub[b][d]));
-        } while ((unsigned)(v >> 32) != epoch);
-        part[d] += (int)(uint32_t)v;
-      }
-    }
+    for (int d = 0; d < kMaxRanks; ++d)
+      if (d < W) part[d] += (int)(uint32_t)layout_wait_pub(&ls->layout_pub[b][d], tag);
   }
 #pragma unroll
   for (int d = 0; d < kMaxRanks; ++d)
@@ -141,7 +161,39 @@ __global__ void __launch_bounds__(256)
   if (bid == (int)gridDim.x - 1 && tid < W) tok_per_rank[tid] = s_base[tid] + s_tile_base[tid];
   for (int e = tid; e < E; e += 256) {
     int h = s_hist[e];
-    if (h) atomicAdd(&tok_per_expert[e], h);
+    if (h) atomicAdd(&ls->layout_hist[e], h);
+  }
+
+  // ---- the last block to finish writes the expert totals, rewinds the scratch and opens the count exchange
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    s_last = atom_add_acq_rel_gpu(&ls->layout_done, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int e = tid; e < E; e += 256) {
+    const int h = __ldcg(&ls->layout_hist[e]);
+    tok_per_expert[e] = h;
+    s_hist[e] = h;
+    if (h) ls->layout_hist[e] = 0;
+  }
+  if (tid < W) s_base[tid] = __ldcg(&tok_per_rank[tid]);
+  if (tid == 0) {
+    ls->layout_ticket = 0;
+    ls->layout_done = 0;
+    volatile unsigned long long* ep = &ls->layout_epoch;  // every block of this call has read it (they have all finished)
+    *ep = *ep + 1;
+  }
+  __syncthreads();
+  if (tail.mode == kTailLocal) {
+    const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) + 1;
+    notify_finish(s_base, 1, s_hist, e_local, 1, 0, tail.slot, e_local, tail.meta, tail.host, epoch);
+    __syncthreads();
+    if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) = epoch;
+  } else if (tail.mode == kTailPublish) {
+    notify_publish(tail.peers, W, tail.me, tail.slot, e_local, s_base, s_hist, tail.epoch_ptr);
   }
 }
 
@@ -149,9 +201,10 @@ __global__ void __launch_bounds__(256)
 
 using namespace b200ep;
 
-extern "C" int b200ep_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
-                             int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
-                             uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream) {
+namespace b200ep {
+int launch_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
+                  int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert, uint8_t* dev_is_token_in_rank,
+                  int32_t* dev_send_off, const NotifyTail& tail, cudaStream_t st) {
   if (!c || T < 0 || K <= 0 || K > kMaxTopk || E <= 0 || E % c->world != 0 || E / c->world > kMaxLocalExperts) {
     set_error("layout: bad shape T=%d K=%d E=%d world=%d", T, K, E, c ? c->world : -1);
     return B200EP_ERR_ARG;
@@ -160,25 +213,17 @@ extern "C" int b200ep_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i6
     set_error("layout: null pointer");
     return B200EP_ERR_ARG;
   }
-  cudaStream_t st = (cudaStream_t)stream;
   B200EP_CUDA(cudaSetDevice(c->device));
-  B200EP_CUDA(cudaMemsetAsync(dev_tokens_per_expert, 0, sizeof(int32_t) * E, st));
-  if (T == 0) {
-    B200EP_CUDA(cudaMemsetAsync(dev_tokens_per_rank, 0, sizeof(int32_t) * c->world, st));
-    return B200EP_OK;
-  }
-  const int ntiles = (T + 255) / 256;
+  // T == 0 still launches one block: it writes the (zero) counts and, with a tail, takes part in the exchange
+  const int ntiles = T > 0 ? (T + 255) / 256 : 1;
   const int tpb = (ntiles + kMaxLayoutBlocks - 1) / kMaxLayoutBlocks;
   const int grid = (ntiles + tpb - 1) / tpb;
-  const unsigned epoch = (unsigned)(++c->layout_epoch);
-  const unsigned long long tbase = c->layout_ticket_base;
-  c->layout_ticket_base += (unsigned long long)grid;
   const size_t smem = sizeof(int) * E;
   const int el = E / c->world;
 #define LAUNCH(IDT, SINGLE)                                                                                      \
   layout_kernel<IDT, SINGLE><<<grid, 256, smem, st>>>((const IDT*)dev_topk_ids, T, K, E, c->world, el,            \
                                                       dev_tokens_per_rank, dev_tokens_per_expert,                 \
-                                                      dev_is_token_in_rank, dev_send_off, c->local, tbase, epoch, tpb)
+                                                      dev_is_token_in_rank, dev_send_off, c->local, tpb, tail)
   if (ids_i64) {
     if (tpb == 1) LAUNCH(int64_t, true); else LAUNCH(int64_t, false);
   } else {
@@ -187,6 +232,16 @@ extern "C" int b200ep_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i6
 #undef LAUNCH
   B200EP_CUDA(cudaGetLastError());
   return B200EP_OK;
+}
+}  // namespace b200ep
+
+extern "C" int b200ep_layout(b200ep_ctx* c, const void* dev_topk_ids, int ids_i64, int T, int K, int E,
+                             int32_t* dev_tokens_per_rank, int32_t* dev_tokens_per_expert,
+                             uint8_t* dev_is_token_in_rank, int32_t* dev_send_off, void* stream) {
+  NotifyTail tail{};
+  tail.mode = kTailNone;
+  return launch_layout(c, dev_topk_ids, ids_i64, T, K, E, dev_tokens_per_rank, dev_tokens_per_expert,
+                       dev_is_token_in_rank, dev_send_off, tail, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -284,11 +339,7 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int d = 0; d < kMaxRanks; ++d) {
       if (d < W) {
-        uint64_t v;
-        do {
-          v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(&sc->pub[b][d]));
-        } while ((v >> 32) == 0);
-        part[d] += (int)(uint32_t)v;
+        part[d] += (int)(uint32_t)layout_wait_pub(&sc->pub[b][d], 1u);
       }
     }
   }

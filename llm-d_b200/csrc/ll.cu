@@ -100,11 +100,14 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
   extern __shared__ __align__(128) char s_mem[];
   __shared__ int s_pos[kMaxTopk];
   __shared__ long long s_myid[kMaxTopk];
+  __shared__ int s_slot[kMaxTopk];  // packed-UE8M0 mode: flat index (e_local * g4) * cap4 + slot of entry k, -1 if none
+  __shared__ int s_dst[kMaxTopk];
   const int tid = threadIdx.x, lane = tid & 31;
   const int W = a.W, K = a.plan.K, H = a.plan.H, e_local = a.plan.e_local, cap = a.plan.cap;
   const int row_bytes = a.plan.row_bytes, scale_bytes = a.plan.scale_bytes;
   char* s_row = s_mem;
   float* s_scale = reinterpret_cast<float*>(s_mem + row_bytes);
+  const bool packed = kFp8 && a.ue8m0 == 2;
   const char* my_base = a.peers.base[a.me];
   const int32_t* cnt = reinterpret_cast<const int32_t*>(my_base + kCtrlLlCntOff) + (size_t)a.slot * kMaxRanks * kLlMaxExperts;
   auto load_id = [&](int t, int k) -> long long {
@@ -222,9 +225,9 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
             char* dst = a.peers.base[d] + a.slot_off;
             const size_t r = (size_t)el * cap + slot_idx;
             bulk_s2g(dst + a.plan.off_x + r * row_bytes, s_row, row_bytes);
-            if (kFp8 && (scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + r * scale_bytes, s_scale, scale_bytes);
+            if (kFp8 && !packed && (scale_bytes & 15) == 0) bulk_s2g(dst + a.plan.off_scales + r * scale_bytes, s_scale, scale_bytes);
             bulk_commit();
-            if (kFp8 && (scale_bytes & 15)) {
+            if (kFp8 && !packed && (scale_bytes & 15)) {
               float* ds = reinterpret_cast<float*>(dst + a.plan.off_scales + r * scale_bytes);
               for (int g = 0; g < scale_bytes / 4; ++g) ds[g] = s_scale[g];
             }
@@ -235,6 +238,26 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
           }
         }
         a.sc->send_slot[t * K + tid] = slot_idx;
+        if (packed) {
+          s_slot[tid] = slot_idx >= 0 ? ((int)(id % e_local) * a.plan.g4) * a.plan.cap4 + slot_idx : -1;
+          s_dst[tid] = slot_idx >= 0 ? (int)(id / e_local) : 0;
+        }
+      }
+      if (kFp8 && packed && have_token) {
+        // Packed UE8M0 scales (what DeepGEMM reads on sm_100, vLLM fp8_utils.py:643-714): the scales are
+        // powers of two, so only the biased exponent byte travels, four groups per int32, written straight
+        // into the owner's [e_local][H/512][slots] array (slot index fastest: "MN-major").
+        __syncthreads();
+        const int g4 = a.plan.g4, ng = scale_bytes / 4;
+        for (int i = tid; i < K * g4; i += blockDim.x) {
+          const int k = i / g4, j = i % g4;
+          if (s_slot[k] < 0) continue;
+          uint32_t wd = 0;
+#pragma unroll
+          for (int b = 0; b < 4; ++b)
+            if (4 * j + b < ng) wd |= ((__float_as_uint(s_scale[4 * j + b]) >> 23) & 0xffu) << (8 * b);
+          reinterpret_cast<uint32_t*>(a.peers.base[s_dst[k]] + a.slot_off + a.plan.off_scales)[(size_t)s_slot[k] + (size_t)j * a.plan.cap4] = wd;
+        }
       }
     }
     if (tid < K) bulk_wait_all();
@@ -285,6 +308,7 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
   const int W = a.W, K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
   char* s_row = s_mem + (size_t)warp * row_bytes;
+  (void)K;
   const int32_t* src_info = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
   // Occupied rows only: exclusive prefix of recv_count over the local experts (one warp, shared memory).
   __shared__ int s_pref[kMaxLocalExperts + 1];
@@ -320,8 +344,8 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
     const int base = s_base;
     if (base >= total) break;
     if (threadIdx.x == 0) s_cta_rows += min(total, base + kGrab) - base;
-    if (warp < kGrab && base + warp < total) {
-      const int r = base + warp;
+    // every grabbed row is pushed: a CTA with fewer than kGrab warps (rows wider than 25 KB) loops
+    for (int r = base + warp; r < min(total, base + kGrab); r += nwarp) {
       {
     int lo = 0, hi = e_local - 1;  // largest el with s_pref[el] <= r
     while (lo < hi) {
@@ -357,7 +381,6 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
       bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + (size_t)flat * row_bytes, s_row, row_bytes);
       bulk_commit();
     }
-    (void)K;
       }
     }
   }

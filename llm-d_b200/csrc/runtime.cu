@@ -104,7 +104,7 @@ static size_t ll_slot_bytes(int max_tok, int H, int W, int E, int use_fp8, int K
   const size_t sc = use_fp8 ? (size_t)H / kGroup * 4 : 0;
   size_t off = 0;
   off = align_up(off + (size_t)e_local * cap * row, 4096);
-  off = align_up(off + (size_t)e_local * cap * sc, 4096);
+  off = align_up(off + (size_t)e_local * (cap + 3) * (sc ? sc : 0), 4096);  // fp32 scales, or packed UE8M0 (never larger)
   off = align_up(off + (size_t)e_local * cap * 4, 4096);
   off = align_up(off + (size_t)max_tok * K * 2 * H, 4096);
   return off;
@@ -128,8 +128,10 @@ int make_ll_plan(const b200ep_ctx* c, int H, int K, int E, int max_tok, int use_
   size_t off = 0;
   p->off_x = off;
   off = align_up(off + (size_t)p->e_local * p->cap * p->row_bytes, 4096);
+  p->g4 = (H / kGroup + 3) / 4;
+  p->cap4 = (p->cap + 3) / 4 * 4;
   p->off_scales = off;
-  off = align_up(off + (size_t)p->e_local * p->cap * p->scale_bytes, 4096);
+  off = align_up(off + (size_t)p->e_local * (p->cap + 3) * p->scale_bytes, 4096);  // fp32 rows, or packed UE8M0 (never larger)
   p->off_src = off;
   off = align_up(off + (size_t)p->e_local * p->cap * 4, 4096);
   p->off_stage = off;
@@ -157,7 +159,21 @@ size_t b200ep_ll_size_hint(int max_tokens_per_rank, int H, int world, int E) {
   return kCtrlBytes + kNumSlots * (ll_slot_bytes(max_tokens_per_rank, H, world, E, 0, kMaxTopk) + 4096);
 }
 
+static void free_ctx(b200ep_ctx* c, cudaError_t* first_err) {
+  auto note = [&](cudaError_t e) {
+    if (e != cudaSuccess && first_err && *first_err == cudaSuccess) *first_err = e;
+  };
+  for (int r = 0; r < c->world; ++r)
+    if (c->ipc_open[r]) note(cudaIpcCloseMemHandle(c->peers.base[r]));
+  if (c->sym) note(cudaFree(c->sym));
+  if (c->local) note(cudaFree(c->local));
+  if (c->ll_local) note(cudaFree(c->ll_local));
+  if (c->host) note(cudaFreeHost((void*)c->host));
+  delete c;
+}
+
 int b200ep_create(b200ep_ctx** out, int rank, int world, int device, size_t sym_bytes) {
+  if (out) *out = nullptr;
   if (!out || world < 1 || world > kMaxRanks || rank < 0 || rank >= world) {
     set_error("create: bad rank/world %d/%d (world <= %d)", rank, world, kMaxRanks);
     return B200EP_ERR_ARG;
@@ -176,21 +192,34 @@ int b200ep_create(b200ep_ctx** out, int rank, int world, int device, size_t sym_
   c->rank = rank;
   c->world = world;
   c->device = device;
-  B200EP_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device));
+  // any failure below frees what was allocated so far (a multi-GB cudaMalloc failing on a GPU whose
+  // memory already belongs to a KV-cache pool is the likely case) and leaves *out null
+#define CREATE_CUDA(call)                                                                            \
+  do {                                                                                               \
+    cudaError_t e_ = (call);                                                                         \
+    if (e_ != cudaSuccess) {                                                                         \
+      set_error("create: %s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      free_ctx(c, nullptr);                                                                          \
+      (void)cudaGetLastError();                                                                      \
+      return B200EP_ERR_CUDA;                                                                        \
+    }                                                                                                \
+  } while (0)
+  CREATE_CUDA(cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, device));
   c->sm_limit = 0;
   c->sym_bytes = sym_bytes / 4096 * 4096;
   c->slot_bytes = (c->sym_bytes - kCtrlBytes) / kNumSlots / 4096 * 4096;
-  B200EP_CUDA(cudaMalloc(&c->sym, c->sym_bytes));
-  B200EP_CUDA(cudaMemset(c->sym, 0, kCtrlBytes));
-  B200EP_CUDA(cudaMalloc(&c->local, sizeof(LocalScratch)));
-  B200EP_CUDA(cudaMemset(c->local, 0, sizeof(LocalScratch)));
+  CREATE_CUDA(cudaMalloc(&c->sym, c->sym_bytes));
+  CREATE_CUDA(cudaMemset(c->sym, 0, kCtrlBytes));
+  CREATE_CUDA(cudaMalloc(&c->local, sizeof(LocalScratch)));
+  CREATE_CUDA(cudaMemset(c->local, 0, sizeof(LocalScratch)));
   c->ll_local_bytes = 4 << 20;
-  B200EP_CUDA(cudaMalloc(&c->ll_local, c->ll_local_bytes));
-  B200EP_CUDA(cudaMemset(c->ll_local, 0, c->ll_local_bytes));
-  B200EP_CUDA(cudaHostAlloc(&c->host, sizeof(HostMirror), cudaHostAllocMapped));
+  CREATE_CUDA(cudaMalloc(&c->ll_local, c->ll_local_bytes));
+  CREATE_CUDA(cudaMemset(c->ll_local, 0, c->ll_local_bytes));
+  CREATE_CUDA(cudaHostAlloc(&c->host, sizeof(HostMirror), cudaHostAllocMapped));
   memset((void*)c->host, 0, sizeof(HostMirror));
-  B200EP_CUDA(cudaHostGetDevicePointer((void**)&c->host_dev, (void*)c->host, 0));
-  B200EP_CUDA(cudaDeviceSynchronize());
+  CREATE_CUDA(cudaHostGetDevicePointer((void**)&c->host_dev, (void*)c->host, 0));
+  CREATE_CUDA(cudaDeviceSynchronize());
+#undef CREATE_CUDA
   c->peers.base[rank] = c->sym;
   c->connected = (world == 1);
   *out = c;
@@ -199,15 +228,14 @@ int b200ep_create(b200ep_ctx** out, int rank, int world, int device, size_t sym_
 
 int b200ep_destroy(b200ep_ctx* c) {
   if (!c) return B200EP_OK;
-  cudaSetDevice(c->device);
-  cudaDeviceSynchronize();
-  for (int r = 0; r < c->world; ++r)
-    if (c->ipc_open[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
-  cudaFree(c->sym);
-  cudaFree(c->local);
-  cudaFree(c->ll_local);
-  cudaFreeHost((void*)c->host);
-  delete c;
+  cudaError_t first = cudaSetDevice(c->device);
+  cudaError_t e = cudaDeviceSynchronize();  // surfaces a kernel that trapped (spin-wait timeout) instead of hiding it
+  if (first == cudaSuccess) first = e;
+  free_ctx(c, &first);
+  if (first != cudaSuccess) {
+    set_error("destroy: %s (everything that could be released was released)", cudaGetErrorString(first));
+    return B200EP_ERR_CUDA;
+  }
   return B200EP_OK;
 }
 

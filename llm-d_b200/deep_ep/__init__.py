@@ -144,7 +144,8 @@ class Buffer:
         with torch.cuda.stream(self._comm):
             lay = self._impl.get_dispatch_layout(topk_idx.contiguous(), num_experts)
         ev = self._leave_comm(compute, async_finish, (topk_idx,))
-        lay.is_token_in_rank._b200ep_layout = lay  # dispatch() needs the prefix offsets too
+        # dispatch() recomputes the layout inside its single C call (a few microseconds of GPU time): nothing
+        # has to be smuggled along on these tensors, and the caller may clone or slice them freely
         return lay.tokens_per_rank, None, lay.tokens_per_expert, lay.is_token_in_rank, ev
 
     def dispatch(self, x, handle=None, num_tokens_per_rank=None, num_tokens_per_rdma_rank=None, is_token_in_rank=None,
@@ -164,14 +165,16 @@ class Buffer:
             xs = xs.contiguous()
         else:
             xq, xs = x, None
-        lay = getattr(is_token_in_rank, "_b200ep_layout", None) if is_token_in_rank is not None else None
-        num_experts = lay.num_experts if lay is not None else int(num_tokens_per_expert.numel())
+        assert num_tokens_per_expert is not None, "b200ep dispatch needs num_tokens_per_expert (its length is the expert count)"
+        num_experts = int(num_tokens_per_expert.numel())
         compute = self._enter_comm(previous_event)
         with torch.cuda.stream(self._comm):
+            # one C call: layout kernel (its last block publishes the counts) -> dispatch kernel (waits for the
+            # peers' counts itself) -> host wait for this rank's row counts, which runs under the dispatch kernel
             rx, rs, ridx, rw, per_expert, h = self._impl.dispatch(
                 xq.contiguous(), topk_idx.contiguous(), None if topk_weights is None else topk_weights.contiguous(),
-                num_experts, x_scales=xs, layout=(None if num_worst_tokens > 0 else lay), quantize=b200ep_quantize,
-                ue8m0=b200ep_ue8m0, num_worst_tokens=num_worst_tokens)
+                num_experts, x_scales=xs, quantize=b200ep_quantize, ue8m0=b200ep_ue8m0,
+                num_worst_tokens=num_worst_tokens)
         ev = self._leave_comm(compute, async_finish, (xq, xs, topk_idx, topk_weights))
         if expert_alignment > 1:
             per_expert = [(n + expert_alignment - 1) // expert_alignment * expert_alignment for n in per_expert]
@@ -195,17 +198,15 @@ class Buffer:
                              round_scale: bool = False, use_ue8m0: bool = False, async_finish: bool = False,
                              return_recv_hook: bool = False, **unsupported):
         if unsupported.get("use_nvfp4"):
-            raise NotImplementedError("b200ep: NVFP4 low-latency dispatch is not implemented (SURVEY.md 8(f) f3)")
+            raise NotImplementedError("b200ep: NVFP4 low-latency dispatch is not implemented (SURVEY.md 8(f) f3); "
+                                      "run vLLM with VLLM_DEEPEPLL_NVFP4_DISPATCH=0 (bf16 dispatch, its default)")
+        # use_ue8m0: packed exponent bytes (one per 128 values, four per int32, slot index fastest -- what DeepGEMM
+        # reads on sm_100, vLLM fp8_utils.py:643-714), written by the dispatch kernel itself; like the payload
+        # they are complete only after hook() when return_recv_hook is set.  round_scale alone: fp32 powers of two.
+        mode = 2 if (use_fp8 and use_ue8m0) else (1 if round_scale else 0)
         px, ps, cnt, h, hook = self._impl.low_latency_dispatch(
             x.contiguous(), topk_idx.contiguous(), num_max_dispatch_tokens_per_rank, num_experts, use_fp8=use_fp8,
-            ue8m0=bool(round_scale or use_ue8m0), return_recv_hook=return_recv_hook)
-        if use_fp8 and use_ue8m0:
-            # packed UE8M0: one exponent byte per scale, four per int32 (vLLM fp8_utils.py:643-714)
-            e = (ps.view(torch.int32) >> 23).to(torch.uint8)
-            pad = (-e.shape[-1]) % 4
-            if pad:
-                e = torch.nn.functional.pad(e, (0, pad))
-            ps = e.contiguous().view(torch.int32)
+            ue8m0=mode, return_recv_hook=return_recv_hook)
         recv_x = (px, ps) if use_fp8 else px
         ev = EventOverlap(self.capture().event if async_finish else None)
         return recv_x, cnt, h, ev, (hook if return_recv_hook else None)

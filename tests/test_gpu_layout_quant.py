@@ -58,6 +58,45 @@ def test_layout_many_tokens_multi_tile(dev):
         buf.destroy()
 
 
+def test_layout_replays_under_a_cuda_graph(dev):
+    """The kernel keeps its call state on the device (tickets, epoch, histogram) and rewinds it itself: a captured
+    launch must give the right answer on every replay, with different ids each time."""
+    from b200ep import Buffer, _lib
+
+    W, E, K, T = 4, 64, 8, 3000
+    buf = Buffer(None, sym_bytes=8 << 20, rank=1, world=W, _connect=False)
+    try:
+        ids = torch.zeros(T, K, dtype=torch.int64, device=dev)
+        tpr = torch.empty(W, dtype=torch.int32, device=dev)
+        tpe = torch.empty(E, dtype=torch.int32, device=dev)
+        inr = torch.empty((T, W), dtype=torch.bool, device=dev)
+        off = torch.empty((T, W), dtype=torch.int32, device=dev)
+        s = torch.cuda.Stream(device=dev)
+
+        def call():
+            _lib.check(buf.lib.b200ep_layout(buf.ctx, ids.data_ptr(), 1, T, K, E, tpr.data_ptr(), tpe.data_ptr(),
+                                             inr.data_ptr(), off.data_ptr(), torch.cuda.current_stream().cuda_stream))
+
+        with torch.cuda.stream(s):
+            call()
+            s.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                call()
+            for rep in range(3):
+                _, new_ids, _ = make_rank_inputs(T, 128, E, K, seed=50 + rep, dist=("uniform", "zipf", "one_rank")[rep], world=W,
+                                                 mask_frac=0.1 * rep)
+                ids.copy_(new_ids.to(dev))
+                g.replay()
+                s.synchronize()
+                want = layout.dispatch_layout(new_ids.numpy(), E, W)
+                assert np.array_equal(tpr.cpu().numpy(), want[0]) and np.array_equal(tpe.cpu().numpy(), want[1])
+                assert np.array_equal(inr.cpu().numpy().astype(np.uint8), want[2])
+                assert np.array_equal(off.cpu().numpy(), want[3])
+    finally:
+        buf.destroy()
+
+
 def _adversarial(H):
     rows = []
     rows.append(np.zeros(H, np.float32))                       # all-zero groups -> eps path

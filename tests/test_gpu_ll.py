@@ -141,3 +141,89 @@ def test_ll_eplb_expert_count_world8():
                 assert np.array_equal(pxh[el, :n], ref[d]["packed_recv_x"][el, :n])
     finally:
         world.destroy()
+
+
+@pytest.mark.parametrize("W,H", [(1, 7168), (2, 2048), (4, 640)])
+def test_ll_packed_ue8m0_scales_written_by_the_kernel(W, H):
+    """use_ue8m0 (DeepEP) / packed UE8M0 (vLLM fp8_utils.py:643-714): power-of-two scales travel as exponent
+    bytes, four per int32, slot index fastest.  Bytes must equal the oracle's pack of the oracle's UE8M0 scales,
+    the payload must equal the UE8M0 quantisation, and the view must have the MN-major strides DeepGEMM checks."""
+    from b200ep import LocalWorld
+
+    E, K, max_tok = 32, 8, 40
+    world = LocalWorld(W, sym_bytes=256 << 20)
+    try:
+        ins = [make_rank_inputs(max_tok - 3 * r, H, E, K, 77 + r, mask_frac=0.1) for r in range(W)]
+        xs, ids = [i[0] for i in ins], [i[1] for i in ins]
+        qs = [fp8.group_quant_fp8(bf16_bits(x), ue8m0=True) for x in xs]
+        ref = dispatch.ll_dispatch([q for q, _ in qs], [i.numpy() for i in ids], E, max_tok, scales=[s for _, s in qs])
+        res = world.low_latency_dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], max_tok, E, use_fp8=True, ue8m0=2)
+        g4, cap = (H // 128 + 3) // 4, W * max_tok
+        for d, (px, ps, cnt, h) in enumerate(res):
+            assert ps.dtype == torch.int32 and tuple(ps.shape) == (E // W, cap, g4)
+            assert ps.stride(1) == 1 and ps.stride(2) == (cap + 3) // 4 * 4 and ps.stride(0) == g4 * ps.stride(2)
+            assert np.array_equal(cnt.cpu().numpy(), ref[d]["recv_count"])
+            pxh, psh = u8(px), ps.cpu().numpy()
+            for el in range(E // W):
+                n = int(ref[d]["recv_count"][el])
+                assert np.array_equal(pxh[el, :n], ref[d]["packed_recv_x"][el, :n])
+                assert np.array_equal(psh[el, :n], fp8.pack_ue8m0(ref[d]["packed_recv_scales"][el, :n]))
+    finally:
+        world.destroy()
+
+
+def test_ll_packed_ue8m0_matches_vllm_packed_quantiser():
+    """Layout AND bytes against vLLM's own packed-UE8M0 quantiser for DeepGEMM
+    (per_token_group_quant_fp8_packed_for_deepgemm, fp8_utils.py:643-714) on the same rows: with one rank and
+    one expert per token every token lands in slot order, so the two [rows, H/512] int32 views must be equal."""
+    try:
+        from vllm.model_executor.layers.quantization.utils.fp8_utils import per_token_group_quant_fp8_packed_for_deepgemm
+    except Exception as e:  # pragma: no cover
+        pytest.skip(f"vLLM packed quantiser not importable: {e}")
+    from b200ep import LocalWorld
+
+    T, H, E = 96, 7168, 1
+    world = LocalWorld(1, sym_bytes=256 << 20)
+    try:
+        x, _, _ = make_rank_inputs(T, H, 8, 1, 5)
+        ids = torch.zeros(T, 1, dtype=torch.int64)
+        (px, ps, cnt, h), = world.low_latency_dispatch([x.to(DEV)], [ids.to(DEV)], T, E, use_fp8=True, ue8m0=2)
+        try:
+            vq, vs = per_token_group_quant_fp8_packed_for_deepgemm(x.to(DEV), 128, use_ue8m0=True)
+        except Exception as e:  # pragma: no cover  (op missing from this vLLM build)
+            pytest.skip(f"vLLM packed quantiser not runnable here: {e}")
+        torch.cuda.synchronize()
+        assert int(cnt[0]) == T
+        assert torch.equal(px[0, :T].view(torch.uint8), vq.view(torch.uint8))
+        assert tuple(vs.shape) == tuple(ps[0, :T].shape) and vs.stride(0) == ps.stride(1) == 1
+        assert torch.equal(ps[0, :T].contiguous(), vs.contiguous())
+    finally:
+        world.destroy()
+
+
+def test_ll_wide_rows_and_eplb_combine():
+    """(a) hidden 16384: a combine CTA then has fewer warps than rows per grab -- every grabbed row must still be
+    pushed; (b) 288 physical experts (36 per rank at EP=8, guides/wide-ep-lws decode.yaml:114-118) through the
+    combine as well."""
+    from b200ep import LocalWorld
+
+    for W, H, E, K, max_tok in ((2, 16384, 16, 4, 24), (8, 256, 288, 8, 16)):
+        world = LocalWorld(W, sym_bytes=(512 << 20) if H > 4096 else (64 << 20))
+        try:
+            ins = [make_rank_inputs(max_tok - r, H, E, K, 900 + r + W) for r in range(W)]
+            xs, ids, ws = [i[0] for i in ins], [i[1] for i in ins], [i[2] for i in ins]
+            xb = [bf16_bits(x) for x in xs]
+            ref = dispatch.ll_dispatch(xb, [i.numpy() for i in ids], E, max_tok)
+            res = world.low_latency_dispatch([x.to(DEV) for x in xs], [i.to(DEV) for i in ids], max_tok, E, use_fp8=False)
+            ys = []
+            for d, (px, ps, cnt, h) in enumerate(res):
+                assert np.array_equal(cnt.cpu().numpy(), ref[d]["recv_count"])
+                y = bits.bf16_to_f32(ref[d]["packed_recv_x"]) * (1.0 + 0.5 * np.arange(E // W, dtype=np.float32))[:, None, None]
+                ys.append(bits.f32_to_bf16(y.reshape(-1, H)).reshape(E // W, W * max_tok, H))
+            outs = world.low_latency_combine([bits_to_bf16(y, DEV) for y in ys], [i.to(DEV) for i in ids],
+                                             [w.to(DEV) for w in ws], [r[-1] for r in res])
+            want = combine.ll_combine(ys, [i.numpy() for i in ids], [w.numpy() for w in ws], ref, E)
+            for r in range(W):
+                assert np.array_equal(bf16_bits(outs[r]), want[r]), f"W={W} H={H}: ll combine differs on rank {r}"
+        finally:
+            world.destroy()

@@ -61,6 +61,38 @@ def test_layout_noalloc_matches_layout_on_two_consecutive_calls():
         buf.destroy()
 
 
+def test_layout_noalloc_matches_the_cpu_oracle_on_a_side_stream():
+    """Same entry point against oracle/layout.py directly (not only against the other CUDA entry point), issued on
+    a stream of the caller's own, for one rank and for eight, with an int64 batch whose last 256-token block is
+    partly empty."""
+    import numpy as np
+
+    from b200ep import _lib
+    from oracle import layout as olayout
+
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(0)
+    side = torch.cuda.Stream(device=dev)
+    g = torch.Generator().manual_seed(7)
+    for W, E, K, T in ((1, 64, 4, 777), (8, 288, 8, 2049)):
+        ids = torch.stack([torch.randperm(E, generator=g)[:K] for _ in range(T)]).to(torch.int64)
+        ids[torch.rand(T, K, generator=g) < 0.1] = -1
+        want = olayout.dispatch_layout(ids.numpy(), E, W)
+        ids = ids.to(dev).contiguous()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):
+            rc, tpr, tpe, inr, off = _call_noalloc(lib, W, ids, E)
+            rc2, tpr2, tpe2, inr2, off2 = _call_noalloc(lib, W, ids, E)  # back to back on the same stream: serialised
+        side.synchronize()
+        assert rc == 0 and rc2 == 0, lib.b200ep_last_error()
+        for got in ((tpr, tpe, inr, off), (tpr2, tpe2, inr2, off2)):
+            assert np.array_equal(got[0].cpu().numpy(), want[0])
+            assert np.array_equal(got[1].cpu().numpy(), want[1])
+            assert np.array_equal(got[2].cpu().numpy().astype(np.uint8), want[2])
+            assert np.array_equal(got[3].cpu().numpy(), want[3])
+
+
 def test_layout_noalloc_rejects_batches_beyond_its_fixed_scratch():
     from b200ep import _lib
 
