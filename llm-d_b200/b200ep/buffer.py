@@ -81,6 +81,34 @@ class LlHandle:
     keep: Any = None
 
 
+class _HtSlotState:
+    __slots__ = ("key", "lay", "lay_ptrs", "el", "n", "n_ref", "pe", "rp", "full", "vcache", "num_recv_dev",
+                 "recv_per_expert_dev")
+
+    def __init__(self, key, lay: Layout, el: int, world: int):
+        self.key, self.lay, self.el = key, lay, el
+        self.lay_ptrs = (lay.tokens_per_rank.data_ptr(), lay.tokens_per_expert.data_ptr(),
+                         lay.is_token_in_rank.data_ptr(), lay.send_off.data_ptr())
+        self.n = C.c_int()
+        self.n_ref = C.byref(self.n)
+        self.pe = (C.c_int32 * el)()
+        self.rp = (C.c_int32 * (world + 1))()
+        self.full = None
+        self.vcache = {}
+        self.num_recv_dev = self.recv_per_expert_dev = None
+
+    def views(self, M: int):
+        """(recv_x, recv_scales, recv_topk_idx, recv_topk_weights, recv_src_idx) narrowed to M rows."""
+        v = self.vcache.get(M)
+        if v is None:
+            fx, fs, fi, fw, fr = self.full[0]
+            assert 0 <= M <= self.full[2]
+            if len(self.vcache) > 64:
+                self.vcache.clear()
+            v = self.vcache[M] = (fx[:M], (None if fs is None else fs[:M]), fi[:M], fw[:M], fr[:M])
+        return v
+
+
 def exchange_handles(group, mine: bytes) -> bytes:
     """All-gather one 64-byte CUDA-IPC handle per rank over a host process group (gloo or nccl);
     returns the world*64-byte blob in rank order.  Same pattern as vLLM's custom all-reduce
@@ -223,6 +251,9 @@ class Buffer:
         """Zero-copy tensors over this rank's receive region (valid until the slot is reused,
         i.e. until the second next dispatch on this Buffer)."""
         M, H, K = h.num_recv, h.H, h.K
+        st = self.__dict__.get("_ht_state", {}).get(h.slot)
+        if st is not None and st.full is not None and st.key[1:5] == (H, K, h.E, h.x_kind):
+            return st.views(M)
         # full-capacity views are built once per (slot, shape): the region layout only depends on them;
         # a call then costs five narrow() ops instead of ~20 tensor ops (the EP=1 step is host bound)
         cache = self.__dict__.setdefault("_view_cache", {})
@@ -277,34 +308,56 @@ class Buffer:
         assert x.is_cuda and x.is_contiguous() and topk_idx.is_contiguous() and topk_idx.shape[0] == T
         assert topk_weights is None or (topk_weights.dtype == torch.float32 and topk_weights.is_contiguous())
         slot = self.next_slot()
-        lay = self._layout_tensors(slot, T, num_experts, x.device)
-        el = num_experts // self.world
-        n = C.c_int()
-        pe = (C.c_int32 * el)()
-        rp = (C.c_int32 * (self.world + 1))()
+        st = self._ht_slot_state(slot, T, H, K, num_experts, kind, x.device)
         nosync = num_worst_tokens > 0
-        L.check(
-            self.lib.b200ep_ht_dispatch_all(
-                self.ctx, slot, _ptr(x), _ptr(x_scales), kind, int(ue8m0), _ptr(topk_idx),
-                int(topk_idx.dtype == torch.int64), _ptr(topk_weights), _ptr(lay.tokens_per_rank),
-                _ptr(lay.tokens_per_expert), _ptr(lay.is_token_in_rank), _ptr(lay.send_off), T, H, K, num_experts,
-                C.byref(n), pe, rp, -1 if nosync else 120000, _stream()),
-            "ht_dispatch_all",
-        )
+        rc = self.lib.b200ep_ht_dispatch_all(
+            self.ctx, slot, x.data_ptr(), _ptr(x_scales), kind, int(ue8m0), topk_idx.data_ptr(),
+            int(topk_idx.dtype == torch.int64), _ptr(topk_weights), st.lay_ptrs[0], st.lay_ptrs[1], st.lay_ptrs[2],
+            st.lay_ptrs[3], T, H, K, num_experts, st.n_ref, st.pe, st.rp, -1 if nosync else 120000, _stream())
+        if rc:
+            L.check(rc, "ht_dispatch_all")
         keep = (x, x_scales, topk_idx, topk_weights)
+        if st.full is None:
+            self._ht_slot_views(st, slot, H, K, kind)
         if nosync:
-            h = HtHandle(slot, T, H, K, num_experts, kind, lay, int(num_worst_tokens), [], keep)
-            v = L.HtView()
-            L.check(self.lib.b200ep_ht_views(self.ctx, slot, C.byref(v)), "ht_views")
-            if num_worst_tokens > v.capacity_rows:
-                raise L.B200EPError(f"num_worst_tokens={num_worst_tokens} exceeds the slot capacity of {v.capacity_rows} rows")
-            devs = self._sym.device
-            prefix = torch.as_tensor(_DevMem(v.rank_prefix, (self.world + 1) * 4), device=devs).view(torch.int32)
-            h.num_recv_dev = prefix[self.world]
-            h.recv_per_expert_dev = torch.as_tensor(_DevMem(v.recv_per_expert, el * 4), device=devs).view(torch.int32)
-            return (*self.ht_views(h)[:4], [], h)
-        h = HtHandle(slot, T, H, K, num_experts, kind, lay, n.value, list(rp), keep)
-        return (*self.ht_views(h)[:4], pe[:], h)
+            if num_worst_tokens > st.full[2]:
+                raise L.B200EPError(f"num_worst_tokens={num_worst_tokens} exceeds the slot capacity of {st.full[2]} rows")
+            h = HtHandle(slot, T, H, K, num_experts, kind, st.lay, int(num_worst_tokens), [], keep)
+            h.num_recv_dev, h.recv_per_expert_dev = st.num_recv_dev, st.recv_per_expert_dev
+            return (*st.views(h.num_recv)[:4], [], h)
+        h = HtHandle(slot, T, H, K, num_experts, kind, st.lay, st.n.value, st.rp[:], keep)
+        return (*st.views(h.num_recv)[:4], st.pe[:], h)
+
+    def _ht_slot_state(self, slot, T, H, K, E, kind, dev):
+        """Everything a dispatch on `slot` needs that does not change from call to call while the shape stays
+        the same: the layout tensors (kept until the matching combine), the ctypes outputs of the C call, the
+        full-capacity views of the receive region.  The EP=1 step is bound by this host code, not by the GPU."""
+        cache = self.__dict__.setdefault("_ht_state", {})
+        key = (T, H, K, E, kind, str(dev))
+        st = cache.get(slot)
+        if st is None or st.key != key:
+            st = _HtSlotState(key, self._layout_tensors(slot, T, E, dev), E // self.world, self.world)
+            cache[slot] = st
+        return st
+
+    def _ht_slot_views(self, st, slot, H, K, kind):
+        v = L.HtView()
+        L.check(self.lib.b200ep_ht_views(self.ctx, slot, C.byref(v)), "ht_views")
+        cap = v.capacity_rows
+        if kind == L.X_BF16:
+            fx = self._view(v.recv_x, cap * 2 * H).view(torch.bfloat16).view(cap, H)
+            fs = None
+        else:
+            fx = self._view(v.recv_x, cap * H).view(torch.float8_e4m3fn).view(cap, H)
+            fs = self._view(v.recv_x_scales, cap * (H // 128) * 4).view(torch.float32).view(cap, H // 128)
+        fi = self._view(v.recv_topk_idx, cap * K * 8).view(torch.int64).view(cap, K)
+        fw = self._view(v.recv_topk_weights, cap * K * 4).view(torch.float32).view(cap, K)
+        fr = self._view(v.recv_src_idx, cap * 4).view(torch.int32)
+        st.full = ((fx, fs, fi, fw, fr), None, cap)
+        devs = self._sym.device
+        prefix = torch.as_tensor(_DevMem(v.rank_prefix, (self.world + 1) * 4), device=devs).view(torch.int32)
+        st.num_recv_dev = prefix[self.world]
+        st.recv_per_expert_dev = torch.as_tensor(_DevMem(v.recv_per_expert, st.el * 4), device=devs).view(torch.int32)
 
     def _layout_tensors(self, slot: int, T: int, E: int, dev) -> Layout:
         """Layout outputs are needed until the matching combine; keep one set per slot and reuse it

@@ -122,6 +122,13 @@ __device__ __forceinline__ void st_na_v4(void* p, const int4& v) {
                "r"(v.w)
                : "memory");
 }
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization
+// attribute may start while its predecessor in the stream is still running; it must not touch anything
+// the predecessor writes before pdl_wait() (which returns when the predecessor has completed and its
+// writes are visible).  The predecessor calls pdl_launch_dependents() to let the dependent grid start
+// early.  Both are no-ops in a normally launched kernel.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // TMA bulk copy shared -> global (local or peer), tracked by the thread's bulk async-group.
@@ -323,8 +330,7 @@ __device__ __forceinline__ float absmax16(const V8& v) {
 // scalar forms): q0 = x*r, e = fma(q0, -s, x), q = fma(e, r, q0).  The sign of a zero quotient
 // (x = -0, or an underflowing negative x) is restored on the e4m3 bytes instead of with one
 // copysign per value: byte |= sign bit of the source bf16.
-__device__ __forceinline__ uint4 quant16(const V8& v, float s) {
-  const float r = __frcp_rn(s);
+__device__ __forceinline__ uint4 quant16(const V8& v, float s, float r) {  // r = RN(1/s)
   const float2 r2 = make_float2(r, r), ns2 = make_float2(-s, -s);
   uint32_t o[4];
 #pragma unroll
@@ -343,6 +349,25 @@ __device__ __forceinline__ uint4 quant16(const V8& v, float s) {
   return make_uint4(o[0], o[1], o[2], o[3]);
 }
 
+__device__ __forceinline__ uint4 quant16(const V8& v, float s) { return quant16(v, s, __frcp_rn(s)); }
+// packed |x| maximum of two vectors (32 values) in one chain, widened once
+__device__ __forceinline__ float absmax32(const V8& a, const V8& b) {
+  __nv_bfloat162 m = __hmax2(__habs2(*reinterpret_cast<const __nv_bfloat162*>(&a.w[0])),
+                             __habs2(*reinterpret_cast<const __nv_bfloat162*>(&b.w[0])));
+#pragma unroll
+  for (int i = 1; i < 8; ++i) {
+    m = __hmax2(m, __habs2(*reinterpret_cast<const __nv_bfloat162*>(&a.w[i])));
+    m = __hmax2(m, __habs2(*reinterpret_cast<const __nv_bfloat162*>(&b.w[i])));
+  }
+  const uint32_t u = *reinterpret_cast<const uint32_t*>(&m);
+  return fmaxf(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+}
+// amax over the 4 lanes that hold one 128-element group (32 values per lane)
+__device__ __forceinline__ float group_amax4(float m) {
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+  return m;
+}
 // amax over the 16 lanes that hold one 128-element group
 __device__ __forceinline__ float group_amax16(float m) {
   m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 8));
@@ -375,7 +400,7 @@ namespace b200ep {
 constexpr int kMaxLayoutBlocks = 1024;
 constexpr int kMaxExperts = kMaxRanks * kMaxLocalExperts;
 struct LocalScratch {
-  unsigned done[64];                                         // CTA-completion counters, one per kernel family
+  unsigned done[128];                                        // CTA-completion counters / work queues, one set per kernel family
   // routing-layout kernel: all of it lives on the device and is rewound by the kernel's last block,
   // so the launch takes no per-call host counter (replays under a CUDA graph)
   unsigned long long layout_ticket;                          // next logical block id of the running call

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256)
     ht_notify_local_kernel(const int32_t* __restrict__ tok_per_rank, const int32_t* __restrict__ tok_per_expert, int slot,
                            int e_local, HtMeta* meta, HostMirror* host, unsigned long long* epoch_ptr) {
   const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
-  notify_finish(tok_per_rank, 1, tok_per_expert, e_local, 1, 0, slot, e_local, meta, host, epoch);
+  notify_finish<false>(tok_per_rank, 1, tok_per_expert, e_local, 1, 0, slot, e_local, meta, host, epoch);
   __syncthreads();
   if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
 }
@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
   const char* my_base = a.peers.base[a.me];
   int n = 0;  // rows this team has staged so far: stage = n % nstage, one bulk group per row and lane
 
+  pdl_wait();  // launched early behind the layout kernel (b200ep_ht_dispatch_all): its outputs are needed from here on
   if (a.prologue) {
     // the peers' counts of THIS call (their layout kernels published them; ours did too, which is
     // what advanced *notify_epoch_ptr): wait, then every CTA derives its own send offsets
@@ -290,55 +291,78 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
 }
 
 // ---- world == 1, quantising kind: rows never leave the GPU, so there is nothing to stage.
-// A warp takes (row, segment of up to 4 x 512 values): four 32-byte loads per lane in flight, the
-// 128-value group is 8 lanes (3 shuffles), e4m3 bytes go out as one 16-byte store per lane (512
-// contiguous bytes per warp) and the group's scale from its first lane.  No shared memory, no
-// barriers: the kernel is bound by HBM (2H in, H + 4H/128 out per token).
-constexpr int kLocalU = 4;
-template <int kH, bool kUe8m0>
-__global__ void __launch_bounds__(256, 3) ht_dispatch_local_kernel(const __grid_constant__ HtDispatchArgs a) {
+// A warp takes (row, segment of up to 2 x 1024 values).  A lane owns 32 CONSECUTIVE values (two 32-byte
+// loads, 64 bytes), so a 128-value group is 4 lanes: two shuffles for the amax, and the scale, its
+// reciprocal and the address arithmetic are paid once per 32 values (with 16 values per lane that
+// per-group overhead was ~40 of ~140 instructions per vector).  e4m3 bytes leave as one 32-byte store
+// per lane (1 KB contiguous per warp), the scale from the group's first lane.  No shared memory, no
+// barriers; one item per warp and as many CTAs as items, so the block scheduler balances the SMs
+// (persistent warps with a static split or an atomic queue and register double-buffering were measured
+// slower: 24.7 / 27.0 us against 22.7 us -- fewer resident warps cost more than the prefetch gains).
+struct V16 {
+  V8 a, b;
+};
+__device__ __forceinline__ void st_v8(void* p, const uint4& lo, const uint4& hi) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
+               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
+               : "memory");
+}
+template <int kH, bool kUe8m0, int kLocalU = 2, int kMinCtas = 3>
+__global__ void __launch_bounds__(256, kMinCtas) ht_dispatch_local_kernel(const __grid_constant__ HtDispatchArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int H = kH > 0 ? kH : a.plan.H, K = a.plan.K;
-  const int nv32 = H / 16, ng = H / kGroup;
-  const int nseg = (nv32 + 32 * kLocalU - 1) / (32 * kLocalU);
+  const int np = H / 32, ng = H / kGroup;  // 64-byte pairs per row, groups per row (4 pairs each)
+  const int nseg = (np + 32 * kLocalU - 1) / (32 * kLocalU);
+  const long long it = (long long)blockIdx.x * 8 + warp;
+  if (it >= (long long)a.T * nseg) return;
+  const int t = (int)(it / nseg), seg = (int)(it % nseg);
+  const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
+  V16 raw[kLocalU];
+#pragma unroll
+  for (int u = 0; u < kLocalU; ++u) {
+    const int p = (seg * kLocalU + u) * 32 + lane;
+    if (p < np) {
+      raw[u].a = ld_nc_v8(src + 2 * p);
+      raw[u].b = ld_nc_v8(src + 2 * p + 1);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) raw[u].a.w[i] = raw[u].b.w[i] = 0u;
+    }
+  }
+  // for the row's first segment, the token's top-k entries: in flight together with the row
+  long long id = -1;
+  float w = 0.f;
+  if (seg == 0 && lane < K) {
+    id = load_topk_id(a.ids, a.ids_i64, (size_t)t * K + lane);
+    w = a.weights ? a.weights[(size_t)t * K + lane] : 0.f;
+  }
+  // Everything above reads the caller's inputs only.  When this kernel was launched early behind the layout
+  // kernel (programmatic dependent launch, b200ep_ht_dispatch_all) its loads are already in flight while the
+  // layout runs; the layout's output -- this token's row, -1 if it has no valid expert -- is read after the wait.
+  pdl_wait();
+  const int row = *reinterpret_cast<const volatile int32_t*>(a.send_off + t);
+  if (row < 0) return;  // uniform over the warp
   char* base = a.peers.base[a.me] + a.slot_off;
-  uint4* out_x = reinterpret_cast<uint4*>(base + a.plan.off_x);
-  float* out_s = reinterpret_cast<float*>(base + a.plan.off_scales);
-  const long long items = (long long)a.T * nseg;
-  for (long long it = (long long)blockIdx.x * 8 + warp; it < items; it += (long long)gridDim.x * 8) {
-    const int t = (int)(it / nseg), seg = (int)(it % nseg);
-    const int row = __ldg(a.send_off + t);  // world 1: the token's row, -1 if it has no valid expert
-    const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.x) + (size_t)t * H);
-    V8 raw[kLocalU];
+  char* out_x = base + a.plan.off_x + (size_t)row * H;
+  float* out_s = reinterpret_cast<float*>(base + a.plan.off_scales) + (size_t)row * ng;
 #pragma unroll
-    for (int u = 0; u < kLocalU; ++u) {
-      const int v = (seg * kLocalU + u) * 32 + lane;
-      if (v < nv32) raw[u] = ld_nc_v8(src + v);
-      else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
-      }
+  for (int u = 0; u < kLocalU; ++u) {
+    const int p = (seg * kLocalU + u) * 32 + lane;
+    if ((seg * kLocalU + u) * 32 >= np) break;  // uniform over the warp
+    const float s = group_scale(group_amax4(absmax32(raw[u].a, raw[u].b)), kUe8m0);
+    const float r = __frcp_rn(s);
+    if (p < np) {
+      st_v8(out_x + (size_t)p * 32, quant16(raw[u].a, s, r), quant16(raw[u].b, s, r));
+      if ((lane & 3) == 0) out_s[p >> 2] = s;
     }
-    if (row < 0) continue;  // uniform over the warp
-#pragma unroll
-    for (int u = 0; u < kLocalU; ++u) {
-      const int v = (seg * kLocalU + u) * 32 + lane;
-      if ((seg * kLocalU + u) * 32 >= nv32) break;  // uniform over the warp
-      const float s = group_scale(group_amax8(absmax16(raw[u])), kUe8m0);
-      if (v < nv32) {
-        out_x[(size_t)row * nv32 + v] = quant16(raw[u], s);
-        if ((lane & 7) == 0) out_s[(size_t)row * ng + (v >> 3)] = s;
-      }
+  }
+  if (seg == 0) {
+    if (lane < K) {
+      const bool mine = id >= 0 && id < a.e_local;
+      reinterpret_cast<long long*>(base + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id : -1;
+      reinterpret_cast<float*>(base + a.plan.off_w)[(size_t)row * K + lane] = mine ? w : 0.f;
     }
-    if (seg == 0) {
-      if (lane < K) {
-        const long long id = load_topk_id(a.ids, a.ids_i64, (size_t)t * K + lane);
-        const bool mine = id >= 0 && id < a.e_local;
-        reinterpret_cast<long long*>(base + a.plan.off_idx)[(size_t)row * K + lane] = mine ? id : -1;
-        reinterpret_cast<float*>(base + a.plan.off_w)[(size_t)row * K + lane] = (mine && a.weights) ? a.weights[(size_t)t * K + lane] : 0.f;
-      }
-      if (lane == 0) reinterpret_cast<int32_t*>(base + a.plan.off_src)[row] = t;
-    }
+    if (lane == 0) reinterpret_cast<int32_t*>(base + a.plan.off_src)[row] = t;
   }
 }
 
@@ -586,29 +610,38 @@ __global__ void __launch_bounds__(256, kMaxSrc == 2 ? 3 : 2) ht_combine_recv_ker
 // world == 1: the combine is a gather of this rank's own result rows, out[t] = bf16(0 + y[row(t)]) (the
 // fp32 accumulate with a single term), zeros for tokens that were sent nowhere.  Same item shape as
 // the local dispatch: (row, segment of 4 x 1 KB), 32-byte loads and stores, four in flight per lane.
-__global__ void __launch_bounds__(256, 4) ht_combine_local_kernel(const __grid_constant__ HtCombineArgs a) {
+constexpr int kCombU = 4;  // 32-byte vectors per lane and item
+template <bool kPersistent>
+__global__ void __launch_bounds__(256, kPersistent ? 3 : 4) ht_combine_local_kernel(const __grid_constant__ HtCombineArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int H = a.plan.H, nv32 = H / 16;
-  const int nseg = (nv32 + 32 * kLocalU - 1) / (32 * kLocalU);
-  const long long items = (long long)a.T * nseg;
-  for (long long it = (long long)blockIdx.x * 8 + warp; it < items; it += (long long)gridDim.x * 8) {
-    const int t = (int)(it / nseg), seg = (int)(it % nseg);
-    const int row = __ldg(a.send_off + t);
+  const int nseg = (nv32 + 32 * kCombU - 1) / (32 * kCombU);
+  const long long items = (long long)a.T * nseg, stride = kPersistent ? (long long)gridDim.x * 8 : items;
+  long long it = (long long)blockIdx.x * 8 + warp;
+  if (it >= items) return;
+  auto load = [&](long long i, V8 (&raw)[kCombU]) {
+    const int row = i < items ? __ldg(a.send_off + (int)(i / nseg)) : -1;
+    const int seg = (int)(i % nseg);
     const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const __nv_bfloat16*>(a.y) + (size_t)(row < 0 ? 0 : row) * H);
-    V8* dst = reinterpret_cast<V8*>(reinterpret_cast<__nv_bfloat16*>(a.out) + (size_t)t * H);
-    V8 raw[kLocalU];
 #pragma unroll
-    for (int u = 0; u < kLocalU; ++u) {
-      const int v = (seg * kLocalU + u) * 32 + lane;
+    for (int u = 0; u < kCombU; ++u) {
+      const int v = (seg * kCombU + u) * 32 + lane;
       if (row >= 0 && v < nv32) raw[u] = ld_nc_v8(src + v);
       else {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) raw[u].w[i] = 0u;
+        for (int i2 = 0; i2 < 8; ++i2) raw[u].w[i2] = 0u;
       }
     }
+  };
+  V8 raw[kCombU], nxt[kCombU];
+  load(it, raw);
+  for (; it < items; it += stride) {
+    const int t = (int)(it / nseg), seg = (int)(it % nseg);
+    if (kPersistent) load(it + stride, nxt);  // next item's loads in flight while this one is converted and stored
+    V8* dst = reinterpret_cast<V8*>(reinterpret_cast<__nv_bfloat16*>(a.out) + (size_t)t * H);
 #pragma unroll
-    for (int u = 0; u < kLocalU; ++u) {
-      const int v = (seg * kLocalU + u) * 32 + lane;
+    for (int u = 0; u < kCombU; ++u) {
+      const int v = (seg * kCombU + u) * 32 + lane;
       if (v >= nv32) continue;
       V8 o;
 #pragma unroll
@@ -622,6 +655,8 @@ __global__ void __launch_bounds__(256, 4) ht_combine_local_kernel(const __grid_c
                    "r"(o.w[1]), "r"(o.w[2]), "r"(o.w[3]), "r"(o.w[4]), "r"(o.w[5]), "r"(o.w[6]), "r"(o.w[7])
                    : "memory");
     }
+#pragma unroll
+    for (int u = 0; u < kCombU; ++u) raw[u] = nxt[u];
   }
 }
 
@@ -792,6 +827,22 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
   return B200EP_OK;
 }
 
+// Launch, optionally as a programmatic dependent of the kernel queued just before it on the stream.
+template <typename Kern, typename Args>
+static cudaError_t launch_kernel(Kern kern, int grid, int block, size_t smem, cudaStream_t st, bool pdl, const Args& a) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, a);
+}
+
 // SEND / RECV launches of the dispatch.  prologue: the kernel itself waits for the peers' counts
 // (production path, b200ep_ht_dispatch_all) instead of relying on an earlier notify-recv launch.
 static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const float* dev_x_scales, int x_kind, int ue8m0,
@@ -850,20 +901,32 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
     a.prologue = (prologue && c->world > 1) ? 1 : 0;
+    // called from b200ep_ht_dispatch_all the layout kernel is queued right in front: start early behind it
+    static const int pdl_env = getenv("B200EP_PDL") ? atoi(getenv("B200EP_PDL")) : 1;
+    const bool pdl = prologue && pdl_env;
     static const int meta_env = getenv("B200EP_HT_META_BULK") ? atoi(getenv("B200EP_HT_META_BULK")) : 1;
     a.meta_bulk = (meta_env && K % 4 == 0 && c->world > 1) ? 1 : 0;
-    if (c->world == 1 && x_kind == B200EP_X_BF16_QUANT && H % 16 == 0) {
+    if (c->world == 1 && x_kind == B200EP_X_BF16_QUANT) {
       // single rank: registers -> receive region, no staging
       a.nstage = 0;
-      const int nseg = (H / 16 + 32 * kLocalU - 1) / (32 * kLocalU);
-      const int grid = grid_for(c, (long long)T * nseg, 8, 3);
+      // one 64-byte pair per lane and item, 6 CTAs per SM (40 registers): measured 18.4 us at 4096 x 7168 against
+      // 20.4 us with two pairs per lane at 3 CTAs per SM -- resident warps matter more than bytes in flight per warp
+      static const int var_env = getenv("B200EP_HT_LOCAL_VAR") ? atoi(getenv("B200EP_HT_LOCAL_VAR")) : 0;
+      const int U = var_env == 1 ? 2 : 1;
+      const int nseg = (H / 32 + 32 * U - 1) / (32 * U);
+      const long long items = (long long)T * nseg;
+      const int grid = (int)((items + 7) / 8 > 0 ? (items + 7) / 8 : 1);
+#define LOCAL_LAUNCH(HH, UE)                                                                                            \
+  do {                                                                                                                  \
+    if (var_env == 1) B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<HH, UE, 2, 4>, grid, 256, 0, st, pdl, a));     \
+    else B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<HH, UE, 1, 6>, grid, 256, 0, st, pdl, a));                 \
+  } while (0)
       if (H == 7168) {
-        if (ue8m0) ht_dispatch_local_kernel<7168, true><<<grid, 256, 0, st>>>(a);
-        else ht_dispatch_local_kernel<7168, false><<<grid, 256, 0, st>>>(a);
+        if (ue8m0) LOCAL_LAUNCH(7168, true); else LOCAL_LAUNCH(7168, false);
       } else {
-        if (ue8m0) ht_dispatch_local_kernel<0, true><<<grid, 256, 0, st>>>(a);
-        else ht_dispatch_local_kernel<0, false><<<grid, 256, 0, st>>>(a);
+        if (ue8m0) LOCAL_LAUNCH(0, true); else LOCAL_LAUNCH(0, false);
       }
+#undef LOCAL_LAUNCH
       B200EP_CUDA(cudaGetLastError());
     } else {
       const size_t meta_off = (size_t)(plan.row_bytes + plan.scale_bytes + 15) / 16 * 16;
@@ -878,8 +941,7 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
       const int grid = grid_for(c, T, kTeams, ctas_per_sm);
       auto launch = [&](auto kern) -> int {
         B200EP_CUDA(ensure_dynamic_smem((const void*)kern, c->device, (int)smem));
-        kern<<<grid, kTeams * kTeamThreads, smem, st>>>(a);
-        B200EP_CUDA(cudaGetLastError());
+        B200EP_CUDA(launch_kernel(kern, grid, kTeams * kTeamThreads, smem, st, pdl, a));
         return B200EP_OK;
       };
       if (x_kind == B200EP_X_BF16_QUANT && H == 7168) rc = launch(ht_dispatch_send_kernel<B200EP_X_BF16_QUANT, 7168>);
@@ -977,8 +1039,11 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
         set_error("ht_combine: y and out must be 32-byte aligned");
         return B200EP_ERR_ARG;
       }
-      const int nseg = (H / 16 + 32 * kLocalU - 1) / (32 * kLocalU);
-      ht_combine_local_kernel<<<grid_for(c, (long long)T * nseg, 8, 4), 256, 0, st>>>(a);
+      const int nseg = (H / 16 + 32 * kCombU - 1) / (32 * kCombU);
+      static const int mode_env = getenv("B200EP_HT_LOCAL_MODE") ? atoi(getenv("B200EP_HT_LOCAL_MODE")) : 1;
+      const long long items = (long long)T * nseg;
+      if (mode_env == 1) ht_combine_local_kernel<false><<<(int)((items + 7) / 8 > 0 ? (items + 7) / 8 : 1), 256, 0, st>>>(a);
+      else ht_combine_local_kernel<true><<<grid_for(c, items, 8, 3), 256, 0, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
     }
     return B200EP_OK;

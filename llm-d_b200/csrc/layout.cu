@@ -53,7 +53,9 @@ __global__ void __launch_bounds__(256)
   __shared__ int s_tile_base[kMaxRanks];
   __shared__ int s_base[kMaxRanks];
   __shared__ unsigned s_bid, s_tag, s_last;
+  __shared__ unsigned s_mask[256];
 
+  pdl_launch_dependents();  // the dispatch kernel may start loading its rows while this kernel runs
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) {
     s_tag = (unsigned)(*reinterpret_cast<volatile unsigned long long*>(&ls->layout_epoch) + 1);
@@ -73,18 +75,24 @@ __global__ void __launch_bounds__(256)
   int my_t = -1;
 
   for (int tile = 0; tile < tiles_per_block; ++tile) {
-    const int t = (bid * tiles_per_block + tile) * 256 + tid;
-    unsigned mask = 0;
-    if (t < T) {
-      const IdT* row = ids + (size_t)t * K;
-      for (int k = 0; k < K; ++k) {
-        long long id = (long long)row[k];
-        if (id >= 0 && id < E) {
-          atomicAdd(&s_hist[(int)id], 1);
-          mask |= 1u << ((int)id / e_local);
-        }
+    const int t_first = (bid * tiles_per_block + tile) * 256;
+    const int t = t_first + tid;
+    // the tile's ids as one coalesced stream of (token, k) entries, several loads in flight per thread;
+    // a token's rank mask is OR-ed together in shared memory (order does not matter)
+    s_mask[tid] = 0u;
+    __syncthreads();
+    const int nent = max(0, min(256, T - t_first)) * K;
+    const IdT* tile_ids = ids + (size_t)t_first * K;
+#pragma unroll 4
+    for (int i = tid; i < nent; i += 256) {
+      const long long id = (long long)tile_ids[i];
+      if (id >= 0 && id < E) {
+        atomicAdd(&s_hist[(int)id], 1);
+        atomicOr(&s_mask[i / K], 1u << ((int)id / e_local));
       }
     }
+    __syncthreads();
+    const unsigned mask = s_mask[tid];
     int wpre[kMaxRanks];
 #pragma unroll
     for (int d = 0; d < kMaxRanks; ++d) {
@@ -189,7 +197,7 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   if (tail.mode == kTailLocal) {
     const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) + 1;
-    notify_finish(s_base, 1, s_hist, e_local, 1, 0, tail.slot, e_local, tail.meta, tail.host, epoch);
+    notify_finish<false>(s_base, 1, s_hist, e_local, 1, 0, tail.slot, e_local, tail.meta, tail.host, epoch);
     __syncthreads();
     if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) = epoch;
   } else if (tail.mode == kTailPublish) {

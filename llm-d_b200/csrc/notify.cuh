@@ -34,17 +34,19 @@ __device__ __forceinline__ void notify_publish(const Peers& peers, int W, int me
 // Derive this rank's receive offsets / totals from the count matrix and post them to the host
 // (one CTA, >= 64 threads).  counts come from the control block (filled by every rank's publish) or,
 // for a single rank, straight from the layout arrays (no exchange, no flags, no fence).
+template <bool kPeerWritten = true>  // true: counts were written by other GPUs into the control block (read through L2)
 __device__ __forceinline__ void notify_finish(const int32_t* cr, int cr_stride, const int32_t* ce, int ce_stride, int W,
                                               int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
                                               unsigned long long epoch) {
   const int tid = threadIdx.x;
   volatile unsigned long long* hw = host->word[slot];
+  auto ld = [](const int32_t* p) -> int { return kPeerWritten ? __ldcg(p) : *p; };  // (__ldcg needs a global address)
   if (tid == 0) {
     int p = 0;
     for (int s = 0; s < W; ++s) {
       meta->rank_prefix[s] = p;
       hw[1 + s] = host_word(epoch, p);
-      p += __ldcg(&cr[s * cr_stride + me]);
+      p += ld(&cr[s * cr_stride + me]);
     }
     meta->rank_prefix[W] = p;
     hw[1 + W] = host_word(epoch, p);
@@ -54,13 +56,13 @@ __device__ __forceinline__ void notify_finish(const int32_t* cr, int cr_stride, 
   if (tid >= 32 && tid < 32 + W) {
     const int d = tid - 32;
     int b = 0;
-    for (int s = 0; s < me; ++s) b += __ldcg(&cr[s * cr_stride + d]);
+    for (int s = 0; s < me; ++s) b += ld(&cr[s * cr_stride + d]);
     meta->send_base[d] = b;
-    meta->send_count[d] = __ldcg(&cr[me * cr_stride + d]);
+    meta->send_count[d] = ld(&cr[me * cr_stride + d]);
   }
   for (int i = tid; i < e_local; i += blockDim.x) {
     int n = 0;
-    for (int s = 0; s < W; ++s) n += __ldcg(&ce[(size_t)s * ce_stride + i]);
+    for (int s = 0; s < W; ++s) n += ld(&ce[(size_t)s * ce_stride + i]);
     meta->recv_per_expert[i] = n;
     hw[1 + kMaxRanks + 1 + i] = host_word(epoch, n);
   }

@@ -324,11 +324,16 @@ int b200ep_ht_notify_wait(b200ep_ctx* c, int slot, int* num_recv_tokens, int32_t
       if (!fresh(1 + kMaxRanks + 1 + i)) return false;
     return true;
   };
+  // The answer normally arrives within microseconds (the kernels are already queued): spin on the mapped words
+  // without giving up the core; look at the clock, the CUDA error state and the scheduler only every 4096 polls.
   auto t0 = std::chrono::steady_clock::now();
-  while (!all_fresh()) {
-    if (timeout_ms > 0 &&
-        std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count() >
-            timeout_ms) {
+  for (unsigned spins = 1; !all_fresh(); ++spins) {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+    if ((spins & 4095u) != 0) continue;
+    const long long ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+    if (timeout_ms > 0 && ms > timeout_ms) {
       set_error("ht_notify_wait: rank %d timed out after %d ms waiting for the count exchange (epoch %llu)", c->rank,
                 timeout_ms, (unsigned long long)want);
       return B200EP_ERR_TIMEOUT;
@@ -339,7 +344,7 @@ int b200ep_ht_notify_wait(b200ep_ctx* c, int slot, int* num_recv_tokens, int32_t
       set_error("ht_notify_wait: CUDA error while waiting: %s", cudaGetErrorString(e));
       return B200EP_ERR_CUDA;
     }
-    std::this_thread::yield();
+    if (ms >= 2) std::this_thread::yield();  // something is slow (a peer is late): stop hogging the core
   }
   std::atomic_thread_fence(std::memory_order_acquire);
   c->host->num_recv_cache[slot] = (int32_t)(uint32_t)hw[0];
