@@ -236,6 +236,92 @@ def run_nccl_agrs(args):
     return 0
 
 
+def run_probe(args):
+    """What NVLink gives SM-driven copies on this box: every rank
+    moves 32 MiB to / from each peer between the symmetric regions, in pieces of the sizes the kernels use
+    (one fp8 row 7 KB, one bf16 row 14 KB, several rows), by TMA bulk copies, by register copies, by peer loads,
+    and with the copy engines.  GB/s per direction per GPU, CUDA events, max time over ranks.  Needs N >= 2."""
+    import ctypes as C
+
+    import torch.distributed as dist
+
+    import b200ep
+    from b200ep import _lib as L
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world < 2:
+        print(json.dumps({"impl": "probe", "unavailable": "needs at least 2 GPUs (torchrun --nproc-per-node N)"}))
+        return 0
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    group = dist.new_group(backend="gloo")
+    bpp = 32 << 20
+    buf = b200ep.Buffer(group, sym_bytes=2 * world * bpp + (4 << 20), device=local, rank=rank, world=world)
+    probe = C.CDLL(os.path.join(os.path.dirname(L.LIB_PATH), "libb200ep_probe.so"))
+    probe.b200ep_probe_run.restype = C.c_int
+    probe.b200ep_probe_run.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+    bases = (C.c_void_p * world)()
+    for r in range(world):
+        p = C.c_void_p()
+        L.check(buf.lib.b200ep_peer_base(buf.ctx, r, C.byref(p)), "peer_base")
+        bases[r] = p.value + (1 << 20)  # skip the control block
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    names = {0: "push_tma", 1: "push_regs", 2: "pull_regs", 3: "pull_tma", 4: "push_copy_engine",
+             5: "push_tma_random_dst", 6: "push_tma_fanout", 7: "push_tma_fanout_small"}
+    cases = []
+    for mode in (0, 3):
+        for piece in (7168, 14336, 28672, 43008):
+            cases.append((mode, piece, sms))
+        cases.append((mode, 14336, 2 * sms))
+        cases.append((mode, 7168, 3 * sms))
+    for mode in (1, 2):
+        for piece in (7168, 14336, 65536):
+            cases.append((mode, piece, 2 * sms))
+    cases.append((4, 16, 1))
+    for mode in (5, 6, 7):
+        cases.append((mode, 7168, sms))
+        cases.append((mode, 7168, 3 * sms))
+    if args.probe_modes:
+        want = {int(m) for m in args.probe_modes.split(",")}
+        cases = [c for c in cases if c[0] in want]
+    st = torch.cuda.current_stream().cuda_stream
+    R = 4
+    out = []
+    for mode, piece, grid in cases:
+        def run():
+            rc = probe.b200ep_probe_run(bases, world, rank, mode, bpp, piece, grid, st)
+            assert rc == 0, f"probe mode {mode} failed: {rc}"
+        run(); run()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(R):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / R], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        moved = (world - 1) * bpp
+        if mode in (6, 7):  # pieces * expected copies (2/3 of the peers), see probe_fanout_kernel
+            npieces = (bpp // piece) * (world - 1) * 3 // (2 * (world - 1)) + 1
+            moved = npieces * piece * (world - 1) * 2 / 3
+        gbs = moved / (float(t.item()) * 1e-3) / 1e9
+        out.append({"mode": names[mode], "piece_bytes": piece if mode != 4 else bpp, "ctas": grid, "ms": float(t.item()), "gbs_per_direction": gbs})
+        if rank == 0:
+            print(f"[probe] {names[mode]:17s} piece {piece:6d} ctas {grid:4d}: {gbs:7.1f} GB/s", file=sys.stderr, flush=True)
+    if rank == 0:
+        print(json.dumps({"impl": "probe", "n_gpus": world, "bytes_per_peer": bpp, "unit": "GB/s per direction per GPU",
+                          "how": "every rank moves 32 MiB to/from each peer at once (permutation order), CUDA events, max over ranks",
+                          "results": out}))
+    torch.cuda.synchronize(); dist.barrier()
+    buf.destroy()
+    dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -247,11 +333,14 @@ def main():
     ap.add_argument("--sym-gb", type=float, default=0.0)
     ap.add_argument("--breakdown", action="store_true", help="per-phase CUDA-event breakdown of the step (stderr)")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed calls (experiments only)")
+    ap.add_argument("--probe-modes", default="", help="--impl probe: comma-separated mode numbers to run (default all)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
     if args.impl == "nccl_agrs":
         return run_nccl_agrs(args)
+    if args.impl == "probe":
+        return run_probe(args)
 
     import torch.distributed as dist
 

@@ -90,6 +90,10 @@ int b200ep_export_handle(b200ep_ctx* ctx, void* out_handle64);
 int b200ep_import_handles(b200ep_ctx* ctx, const void* handles, int n);
 int b200ep_set_peer_ptrs(b200ep_ctx* ctx, void* const* dev_bases, int n);
 int b200ep_sym_base(b200ep_ctx* ctx, void** dev_base, size_t* bytes);
+/* Address at which rank `rank`'s symmetric region is mapped in THIS process (its own base for rank == ctx rank);
+ * valid once the peers are connected.  DeepEP keeps the equivalent table private (buffer_ptrs); it is exposed here
+ * for tools that move data between the regions themselves (bench.py --impl probe). */
+int b200ep_peer_base(b200ep_ctx* ctx, int rank, void** dev_base);
 /* Replaces deep_ep.Buffer.set_num_sms (all2all.py:247-255): upper bound on the
  * CTAs the data-moving kernels launch (0 = one wave over all SMs). */
 int b200ep_set_num_sms(b200ep_ctx* ctx, int num_sms);

@@ -60,6 +60,7 @@ SIGNATURES = {
     "b200ep_import_handles": (_i, [_p, _p, _i]),
     "b200ep_set_peer_ptrs": (_i, [_p, C.POINTER(_p), _i]),
     "b200ep_sym_base": (_i, [_p, C.POINTER(_p), C.POINTER(_sz)]),
+    "b200ep_peer_base": (_i, [_p, _i, C.POINTER(_p)]),
     "b200ep_set_num_sms": (_i, [_p, _i]),
     "b200ep_layout": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "b200ep_layout_noalloc": (_i, [_i, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),

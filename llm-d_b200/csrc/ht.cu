@@ -82,6 +82,7 @@ struct HtDispatchArgs {
   int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
   int prologue;   // 1: wait for the peers' counts and derive the offsets here (no notify-recv launch)
   int meta_bulk;  // 1: top-k ids / weights rows travel as TMA bulk copies too (K % 4 == 0)
+  int dbg;        // timing experiments only (B200EP_HT_DBG, results are wrong): 1 = payload rows only, 2 = no copies to this rank itself
 };
 
 constexpr int kTeamThreads = 128;  // a team of 4 warps moves one row at a time
@@ -262,7 +263,18 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
     fence_proxy_async_smem();
     team_bar(team);
     if (twarp == 0) {
-      if (my_in) {
+      if (my_in && a.dbg) {
+        if (!((a.dbg & 2) && lane == a.me)) {
+          char* dst = a.peers.base[lane] + a.slot_off;
+          bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
+          if (!(a.dbg & 1)) {
+            bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
+            bulk_s2g(dst + a.plan.off_idx + (size_t)my_row * K * 8, s_meta + (size_t)lane * K * 8, K * 8);
+            bulk_s2g(dst + a.plan.off_w + (size_t)my_row * K * 4, s_meta + (size_t)W * K * 8 + (size_t)lane * K * 4, K * 4);
+            *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+          }
+        }
+      } else if (my_in) {
         char* dst = a.peers.base[lane] + a.slot_off;
         bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
         if (scale_bytes && (scale_bytes & 15) == 0)
@@ -403,6 +415,12 @@ __device__ __forceinline__ size_t stage_row_off(const HtPlan& p, int d, int pos,
 // at least g - kDmaAhead stores are committed, so "at most kDmaStages - kDmaAhead - 1 pending" covers store g - kDmaStages.
 constexpr int kDmaStages = 4;
 constexpr int kDmaAhead = 2;
+// After every store the driver waits until at most kDmaPending of its groups are still incomplete: with 2-row
+// pieces that is > 100 KB per SM on the wire (the fabric needs ~25 KB per SM), so it never starves the link, and
+// it makes "piece number stores - kDmaPending and everything older has LANDED" known at every step -- which is
+// what the per-chunk flags of the overlapped combine need.  (Waiting only at chunk boundaries, down to two
+// pending groups, drained the pipeline eight times per call: 470 us against 410 us for the push alone at EP=8.)
+constexpr int kDmaPending = 4;
 struct DmaPipe {
   char* stage;
   uint64_t* bar;
@@ -424,7 +442,10 @@ __device__ __forceinline__ void dma_store(DmaPipe& p) {
   mbar_wait(&p.bar[st], (unsigned)(g / kDmaStages) & 1u);
   bulk_s2g(p.dst[st], p.stage + (size_t)st * p.stage_bytes, p.bytes[st]);
   bulk_commit();
+  bulk_wait<kDmaPending>();
 }
+// pieces known to have landed (all of this thread's stores older than the kDmaPending most recent ones)
+__device__ __forceinline__ int dma_landed(const DmaPipe& p) { return p.stores - kDmaPending; }
 
 // Row ranges of chunk c (source tokens [c*512, (c+1)*512), the last chunk takes the rest) inside every
 // remote source's block of this rank's receive order: s_lo[k][c] for source (me+1+k) % W.
@@ -451,8 +472,9 @@ __device__ __forceinline__ void combine_chunk_bounds(const HtCombineArgs& a, con
 // The driver thread's part of chunk c for CTA `cta` of `nctas`: pieces interleave the remote sources
 // starting at rank me+1, so that at any moment the W ranks push along a permutation (all ranks
 // converging on rank 0 first was measured 2.2x slower).  Returns the number of pieces stored.
+template <typename AfterStore>
 __device__ __forceinline__ int combine_push_chunk(const HtCombineArgs& a, DmaPipe& p, int (*s_lo)[kCombChunks + 1], int c,
-                                                  int cta, int nctas) {
+                                                  int cta, int nctas, AfterStore after_store) {
   const int W = a.W, R = a.rows_per_piece, row_bytes = 2 * a.plan.H;
   int maxp = 0;
   for (int k = 0; k < W - 1; ++k) maxp = max(maxp, (s_lo[k][c + 1] - s_lo[k][c] + R - 1) / R);
@@ -483,6 +505,7 @@ __device__ __forceinline__ int combine_push_chunk(const HtCombineArgs& a, DmaPip
     if (stored < loaded) {
       dma_store(p);
       ++stored;
+      after_store();
     } else if (!more) {
       break;
     }
@@ -508,7 +531,7 @@ __global__ void __launch_bounds__(128, 1) ht_combine_send_kernel(const __grid_co
     p.bar = s_bar;
     p.stage_bytes = a.stage_bytes;
     p.loads = p.stores = 0;
-    for (int c = 0; c < kCombChunks; ++c) combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x);
+    for (int c = 0; c < kCombChunks; ++c) combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x, []() {});
     bulk_wait_all();
   }
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, a.W, kFlagHtComb, a.slot, a.me);
@@ -704,16 +727,16 @@ __global__ void __launch_bounds__(512, 1) ht_combine_fused_kernel(const __grid_c
             st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), want);
       }
     };
+    int end_seq[kCombChunks];  // stores issued by the end of chunk c: chunk c has landed once dma_landed() >= end_seq[c]
+    int next_arrive = 0;
     for (int c = 0; c < kCombChunks; ++c) {
-      const int issued = combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x);
-      if (c > 0) {
-        // everything older than this chunk's most recent groups has landed -> chunk c-1 is complete here
-        if (issued >= 2) bulk_wait<2>(); else bulk_wait_all();
-        arrive(c - 1);
-      }
+      combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x, [&]() {
+        while (next_arrive < c && end_seq[next_arrive] <= dma_landed(p)) arrive(next_arrive++);
+      });
+      end_seq[c] = p.stores;
     }
     bulk_wait_all();
-    arrive(kCombChunks - 1);
+    while (next_arrive < kCombChunks) arrive(next_arrive++);
   }
   __syncwarp();
 
@@ -906,6 +929,8 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     const bool pdl = prologue && pdl_env;
     static const int meta_env = getenv("B200EP_HT_META_BULK") ? atoi(getenv("B200EP_HT_META_BULK")) : 1;
     a.meta_bulk = (meta_env && K % 4 == 0 && c->world > 1) ? 1 : 0;
+    static const int dbg_env = getenv("B200EP_HT_DBG") ? atoi(getenv("B200EP_HT_DBG")) : 0;
+    a.dbg = dbg_env;
     if (c->world == 1 && x_kind == B200EP_X_BF16_QUANT) {
       // single rank: registers -> receive region, no staging
       a.nstage = 0;
@@ -1021,8 +1046,9 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.chunk_done = &c->local->done[16 + slot * kCombChunks];
   a.red_next = &c->local->done[32 + slot * 16];
   const int row_bytes = 2 * H;
-  // DMA pieces: as many whole rows as fit 44 KB (4 stages of it stay within one SM's shared memory)
-  a.rows_per_piece = 44 * 1024 / row_bytes;
+  // DMA pieces: as many whole rows as fit 29 KB (two DeepSeek rows; the probe gives 672 GB/s for 28 KB pieces and
+  // 677 GB/s for 42 KB ones at EP=8, and smaller pieces make the per-chunk flags of the overlapped kernel timelier)
+  a.rows_per_piece = 29 * 1024 / row_bytes;
   if (a.rows_per_piece < 1) a.rows_per_piece = 1;
   static const int piece_env = getenv("B200EP_HT_PIECE_ROWS") ? atoi(getenv("B200EP_HT_PIECE_ROWS")) : 0;
   if (piece_env > 0 && piece_env < a.rows_per_piece) a.rows_per_piece = piece_env;

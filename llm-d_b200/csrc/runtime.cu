@@ -292,6 +292,19 @@ int b200ep_sym_base(b200ep_ctx* c, void** dev_base, size_t* bytes) {
   return B200EP_OK;
 }
 
+int b200ep_peer_base(b200ep_ctx* c, int rank, void** dev_base) {
+  if (!c || !dev_base || rank < 0 || rank >= c->world) {
+    set_error("peer_base: bad argument");
+    return B200EP_ERR_ARG;
+  }
+  if (!c->connected) {
+    set_error("peer_base: peers not connected");
+    return B200EP_ERR_STATE;
+  }
+  *dev_base = c->peers.base[rank];
+  return B200EP_OK;
+}
+
 int b200ep_set_num_sms(b200ep_ctx* c, int num_sms) {
   if (!c || num_sms < 0) {
     set_error("set_num_sms: bad argument");
