@@ -57,6 +57,8 @@ struct Peers {
 // Region layout of one high-throughput slot (identical on every rank).
 struct HtPlan {
   size_t off_x, off_scales, off_idx, off_w, off_src, off_stage;
+  size_t off_side;      // [cap_rows][side_bytes]: what travels with a row besides its payload (see ht.cu)
+  int side_bytes;       // K*12 + 4 + scale_bytes rounded up to 16
   size_t off_qstage;    // local only: quantised rows [t_cap][qrow_bytes] staged before the ordered push
   size_t off_sendlist;  // local only: int32 [world][t_cap], token sent to rank d at position p
   int qrow_bytes;       // row_bytes + scale_bytes rounded up to 16

@@ -81,9 +81,17 @@ struct HtDispatchArgs {
   const unsigned long long* notify_epoch_ptr;     // count flags (prologue)
   int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
   int prologue;   // 1: wait for the peers' counts and derive the offsets here (no notify-recv launch)
-  int meta_bulk;  // 1: top-k ids / weights rows travel as TMA bulk copies too (K % 4 == 0)
-  int dbg;        // timing experiments only (B200EP_HT_DBG, results are wrong): 1 = payload rows only, 2 = no copies to this rank itself
 };
+
+// What travels with a row besides its payload, as ONE record of plan.side_bytes (16-byte multiple), identical
+// for every destination: [ top-k ids K x i64 (global) | top-k weights K x f32 | source token i32 | scales ].
+// The sender stages it next to the row and issues exactly two TMA bulk copies per (row, destination); the
+// receiver's wait kernel unpacks the records into the contiguous recv_topk_idx (destination-local ids, -1
+// elsewhere) / recv_topk_weights (0 elsewhere) / recv_src_idx / recv_x_scales arrays vLLM reads.  (Per
+// destination three more small bulk copies or plain stores cost ~6 % of the push: fabric probe, 625 vs 667 GB/s.)
+__host__ __device__ inline int side_w_off(int K) { return K * 8; }
+__host__ __device__ inline int side_src_off(int K) { return K * 12; }
+__host__ __device__ inline int side_scale_off(int K) { return K * 12 + 4; }
 
 constexpr int kTeamThreads = 128;  // a team of 4 warps moves one row at a time
 constexpr int kTeams = 4;          // teams per CTA (512 threads); one sys-scope fence per CTA at the end
@@ -156,8 +164,8 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
   const int W = a.W, K = a.plan.K, H = kH > 0 ? kH : a.plan.H;
   const int row_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH : a.plan.row_bytes;
   const int scale_bytes = (kH > 0 && KIND == B200EP_X_BF16_QUANT) ? kH / kGroup * 4 : a.plan.scale_bytes;
-  const int meta_off = (row_bytes + scale_bytes + 15) / 16 * 16;
-  const int stage_bytes = (meta_off + (a.meta_bulk ? W * K * 12 : 0) + 127) / 128 * 128;
+  const int side_bytes = (K * 12 + 4 + scale_bytes + 15) / 16 * 16;
+  const int stage_bytes = (row_bytes + side_bytes + 127) / 128 * 128;
   char* s_team = s_mem + (size_t)team * a.nstage * stage_bytes;
   const int in_row_bytes = KIND == B200EP_X_BF16_QUANT ? 2 * H : row_bytes;
   const int nvec = in_row_bytes / 16;
@@ -202,8 +210,8 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
     }
 
     char* s_row = s_team + (size_t)(a.nstage == 2 ? (n & 1) : 0) * stage_bytes;
-    float* s_scale = reinterpret_cast<float*>(s_row + row_bytes);
-    char* s_meta = s_row + meta_off;
+    char* s_side = s_row + row_bytes;
+    float* s_scale = reinterpret_cast<float*>(s_side + side_scale_off(K));
     ++n;
     if (KIND == B200EP_X_BF16_QUANT) {
       const V8* src = reinterpret_cast<const V8*>(reinterpret_cast<const char*>(a.x) + (size_t)t * in_row_bytes);
@@ -237,65 +245,22 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
       const int ng = H / kGroup;
       for (int g = ttid; g < ng; g += kTeamThreads) s_scale[g] = a.x_scales[(size_t)t * ng + g];
     }
-    if (twarp == 1) {
-      // top-k ids -> destination-local ids; weights zeroed where the expert lives elsewhere
-      const int owner = id >= 0 ? (int)(id / a.e_local) : -1;
-      for (int d = 0; d < W; ++d) {
-        if (!((dmask >> d) & 1u)) continue;
-        const bool mine = owner == d;
-        const long long lid = mine ? id - (long long)d * a.e_local : -1;
-        const float lw = mine ? w : 0.f;
-        if (a.meta_bulk) {
-          if (lane < K) {
-            reinterpret_cast<long long*>(s_meta)[d * K + lane] = lid;
-            reinterpret_cast<float*>(s_meta + (size_t)W * K * 8)[d * K + lane] = lw;
-          }
-        } else {
-          const int row = __shfl_sync(0xffffffffu, my_row, d);
-          if (lane < K) {
-            char* dst = a.peers.base[d] + a.slot_off;
-            reinterpret_cast<long long*>(dst + a.plan.off_idx)[(size_t)row * K + lane] = lid;
-            reinterpret_cast<float*>(dst + a.plan.off_w)[(size_t)row * K + lane] = lw;
-          }
-        }
+    if (twarp == 1) {  // the rest of the side record: ids and weights as they are, and the source token
+      if (lane < K) {
+        reinterpret_cast<long long*>(s_side)[lane] = id;
+        reinterpret_cast<float*>(s_side + side_w_off(K))[lane] = w;
       }
+      if (lane == 0) *reinterpret_cast<int32_t*>(s_side + side_src_off(K)) = t;
     }
     fence_proxy_async_smem();
     team_bar(team);
     if (twarp == 0) {
-      if (my_in && a.dbg) {
-        if (!((a.dbg & 2) && lane == a.me)) {
-          char* dst = a.peers.base[lane] + a.slot_off;
-          bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
-          if (!(a.dbg & 1)) {
-            bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
-            bulk_s2g(dst + a.plan.off_idx + (size_t)my_row * K * 8, s_meta + (size_t)lane * K * 8, K * 8);
-            bulk_s2g(dst + a.plan.off_w + (size_t)my_row * K * 4, s_meta + (size_t)W * K * 8 + (size_t)lane * K * 4, K * 4);
-            *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
-          }
-        }
-      } else if (my_in) {
+      if (my_in) {
         char* dst = a.peers.base[lane] + a.slot_off;
         bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
-        if (scale_bytes && (scale_bytes & 15) == 0)
-          bulk_s2g(dst + a.plan.off_scales + (size_t)my_row * scale_bytes, s_scale, scale_bytes);
-        if (a.meta_bulk) {
-          bulk_s2g(dst + a.plan.off_idx + (size_t)my_row * K * 8, s_meta + (size_t)lane * K * 8, K * 8);
-          bulk_s2g(dst + a.plan.off_w + (size_t)my_row * K * 4, s_meta + (size_t)W * K * 8 + (size_t)lane * K * 4, K * 4);
-        }
-        *reinterpret_cast<int32_t*>(dst + a.plan.off_src + (size_t)my_row * 4) = t;
+        bulk_s2g(dst + a.plan.off_side + (size_t)my_row * side_bytes, s_side, side_bytes);
       }
       bulk_commit();  // every lane, every row (possibly empty): group count == rows staged
-      if (scale_bytes && (scale_bytes & 15)) {  // scale vector not a 16-byte multiple: plain stores
-        const int ng = scale_bytes / 4;
-        for (int d = 0; d < W; ++d) {
-          if (!((dmask >> d) & 1u)) continue;
-          const int row = __shfl_sync(0xffffffffu, my_row, d);
-          float* dsts = reinterpret_cast<float*>(a.peers.base[d] + a.slot_off + a.plan.off_scales + (size_t)row * scale_bytes);
-          for (int g = lane; g < ng; g += 32) dsts[g] = s_scale[g];
-        }
-        __syncwarp();
-      }
     }
   }
   if ((ttid >> 5) == 0) bulk_wait_all();
@@ -378,9 +343,45 @@ __global__ void __launch_bounds__(256, kMinCtas) ht_dispatch_local_kernel(const 
   }
 }
 
-__global__ void wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
-                                    const unsigned long long* epoch_ptr) {
-  cta_wait_all_sources(my_base, W, cat, slot, me, epoch_ptr);
+// RECV phase of the dispatch: wait until every source rank's rows have landed, then unpack the side
+// records of the rows received into the contiguous arrays the caller reads (the number of rows is
+// read on the device, so the host-sync-free form needs nothing from the host).
+struct HtRecvArgs {
+  HtPlan plan;
+  char* my_base;  // this rank's region
+  size_t slot_off;
+  const HtMeta* meta;
+  const unsigned long long* epoch_ptr;
+  int W, me, slot, e_local;
+};
+__global__ void __launch_bounds__(256) ht_dispatch_recv_kernel(const __grid_constant__ HtRecvArgs a) {
+  if (a.W > 1) cta_wait_all_sources(a.my_base, a.W, kFlagHtData, a.slot, a.me, a.epoch_ptr);
+  const int K = a.plan.K, ng = a.plan.scale_bytes / 4, side_bytes = a.plan.side_bytes;
+  char* base = a.my_base + a.slot_off;
+  const char* side0 = base + a.plan.off_side;
+  const long long M = *reinterpret_cast<const volatile int32_t*>(&a.meta->num_recv);
+  // flat index spaces, one element per thread and step: every load is independent of the others
+  const long long me_g = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  long long* out_idx = reinterpret_cast<long long*>(base + a.plan.off_idx);
+  float* out_w = reinterpret_cast<float*>(base + a.plan.off_w);
+  for (long long i = me_g; i < M * K; i += nth) {
+    const long long row = i / K;
+    const int k = (int)(i % K);
+    const char* side = side0 + (size_t)row * side_bytes;
+    const long long id = __ldcg(reinterpret_cast<const long long*>(side) + k);
+    const float w = __ldcg(reinterpret_cast<const float*>(side + side_w_off(K)) + k);
+    const bool mine = id >= 0 && (int)(id / a.e_local) == a.me;
+    out_idx[i] = mine ? id - (long long)a.me * a.e_local : -1;
+    out_w[i] = mine ? w : 0.f;
+  }
+  float* out_s = reinterpret_cast<float*>(base + a.plan.off_scales);
+  for (long long i = me_g; i < M * ng; i += nth) {
+    const long long row = i / ng;
+    out_s[i] = __ldcg(reinterpret_cast<const float*>(side0 + (size_t)row * side_bytes + side_scale_off(K)) + (int)(i % ng));
+  }
+  int32_t* out_src = reinterpret_cast<int32_t*>(base + a.plan.off_src);
+  for (long long i = me_g; i < M; i += nth)
+    out_src[i] = __ldcg(reinterpret_cast<const int32_t*>(side0 + (size_t)i * side_bytes + side_src_off(K)));
 }
 
 // ------------------------------------------------------------------ combine
@@ -927,10 +928,6 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     // called from b200ep_ht_dispatch_all the layout kernel is queued right in front: start early behind it
     static const int pdl_env = getenv("B200EP_PDL") ? atoi(getenv("B200EP_PDL")) : 1;
     const bool pdl = prologue && pdl_env;
-    static const int meta_env = getenv("B200EP_HT_META_BULK") ? atoi(getenv("B200EP_HT_META_BULK")) : 1;
-    a.meta_bulk = (meta_env && K % 4 == 0 && c->world > 1) ? 1 : 0;
-    static const int dbg_env = getenv("B200EP_HT_DBG") ? atoi(getenv("B200EP_HT_DBG")) : 0;
-    a.dbg = dbg_env;
     if (c->world == 1 && x_kind == B200EP_X_BF16_QUANT) {
       // single rank: registers -> receive region, no staging
       a.nstage = 0;
@@ -954,8 +951,7 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
 #undef LOCAL_LAUNCH
       B200EP_CUDA(cudaGetLastError());
     } else {
-      const size_t meta_off = (size_t)(plan.row_bytes + plan.scale_bytes + 15) / 16 * 16;
-      const size_t stage_bytes = (meta_off + (a.meta_bulk ? (size_t)c->world * K * 12 : 0) + 127) / 128 * 128;
+      const size_t stage_bytes = (size_t)(plan.row_bytes + plan.side_bytes + 127) / 128 * 128;
       const int ctas_per_sm = x_kind == B200EP_X_BF16_QUANT ? 3 : 2;
       a.nstage = 2 * kTeams * stage_bytes * ctas_per_sm <= 216 * 1024 ? 2 : 1;  // every resident CTA must still fit
       const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
@@ -976,9 +972,28 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
       if (rc) return rc;
     }
   }
-  if ((phases & B200EP_PHASE_RECV) && c->world > 1) {  // a single rank has nobody to wait for
-    wait_sources_kernel<<<1, 32, 0, st>>>(c->sym, c->world, kFlagHtData, slot, c->rank, &c->local->epoch[kFlagHtData][slot]);
-    B200EP_CUDA(cudaGetLastError());
+  if (phases & B200EP_PHASE_RECV) {
+    const HtPlan& plan = c->ht_plan[slot];
+    if (plan.H == 0) {
+      set_error("ht_dispatch: RECV phase without a SEND phase on slot %d", slot);
+      return B200EP_ERR_STATE;
+    }
+    // the single-rank quantising kernel writes the final arrays itself: nothing to wait for, nothing to unpack
+    if (!(c->world == 1 && plan.x_kind == B200EP_X_BF16_QUANT)) {
+      HtRecvArgs r;
+      r.plan = plan;
+      r.my_base = c->sym;
+      r.slot_off = kCtrlBytes + (size_t)slot * c->slot_bytes;
+      r.meta = &c->local->ht[slot];
+      r.epoch_ptr = &c->local->epoch[kFlagHtData][slot];
+      r.W = c->world;
+      r.me = c->rank;
+      r.slot = slot;
+      r.e_local = E / c->world;
+      // rows are counted on the device (they do not depend on what THIS rank sent): two CTAs per SM stride over them
+      ht_dispatch_recv_kernel<<<grid_for(c, 1LL << 40, 8, 2), 256, 0, st>>>(r);
+      B200EP_CUDA(cudaGetLastError());
+    }
   }
   return B200EP_OK;
 }

@@ -60,10 +60,11 @@ int make_ht_plan(const b200ep_ctx* c, int H, int K, int x_kind, HtPlan* p) {
   p->x_kind = x_kind;
   p->row_bytes = x_kind == B200EP_X_BF16 ? 2 * H : H;
   p->scale_bytes = x_kind == B200EP_X_BF16 ? 0 : H / kGroup * 4;
-  const size_t per_recv_row = (size_t)p->row_bytes + p->scale_bytes + (size_t)K * 12 + 4;
+  p->side_bytes = (K * 12 + 4 + p->scale_bytes + 15) / 16 * 16;
+  const size_t per_recv_row = (size_t)p->row_bytes + p->scale_bytes + (size_t)K * 12 + 4 + p->side_bytes;
   p->qrow_bytes = (p->row_bytes + p->scale_bytes + 15) / 16 * 16;
   const size_t per_token = (size_t)W * per_recv_row + (size_t)W * 2 * H + (size_t)p->qrow_bytes + (size_t)W * 4;
-  const size_t slack = 12 * 4096;
+  const size_t slack = 13 * 4096;
   if (c->slot_bytes <= slack) {
     set_error("ht: symmetric region too small");
     return B200EP_ERR_CAPACITY;
@@ -84,6 +85,8 @@ int make_ht_plan(const b200ep_ctx* c, int H, int K, int x_kind, HtPlan* p) {
   off = align_up(off + (size_t)p->cap_rows * K * 4, 4096);
   p->off_src = off;
   off = align_up(off + (size_t)p->cap_rows * 4, 4096);
+  p->off_side = off;
+  off = align_up(off + (size_t)p->cap_rows * p->side_bytes, 4096);
   p->off_stage = off;
   off = align_up(off + (size_t)p->t_cap * W * 2 * H, 4096);
   p->off_qstage = off;
