@@ -94,6 +94,10 @@ int b200ep_sym_base(b200ep_ctx* ctx, void** dev_base, size_t* bytes);
  * valid once the peers are connected.  DeepEP keeps the equivalent table private (buffer_ptrs); it is exposed here
  * for tools that move data between the regions themselves (bench.py --impl probe). */
 int b200ep_peer_base(b200ep_ctx* ctx, int rank, void** dev_base);
+/* Measurement aid, no DeepEP counterpart: with B200EP_TRACE=1 in the environment the kernels record
+ * %globaltimer stamps (ns) of their phases in the context's private scratch; this copies the 128 slots out
+ * (synchronous; indices are listed in tools/trace_report.py). */
+int b200ep_debug_trace(b200ep_ctx* ctx, unsigned long long* out128);
 /* Replaces deep_ep.Buffer.set_num_sms (all2all.py:247-255): upper bound on the
  * CTAs the data-moving kernels launch (0 = one wave over all SMs). */
 int b200ep_set_num_sms(b200ep_ctx* ctx, int num_sms);
@@ -152,7 +156,7 @@ int b200ep_ht_capacity(b200ep_ctx* ctx, int H, int K, int x_kind);
 
 /* Count exchange that opens a dispatch (DeepEP notify_dispatch, inside
  * deep_ep.Buffer.dispatch, deepep_ht.py:139-162).
- * SEND: publish this rank's per-rank / per-expert counts to every peer.
+ * SEND: publish this rank's per-rank / per-expert counts and its token count T to every peer.
  * RECV: wait for all peers, derive receive offsets and per-expert totals and
  *       post them to pinned host memory.
  * b200ep_ht_notify_wait then blocks the HOST until RECV has run and returns
@@ -160,7 +164,7 @@ int b200ep_ht_capacity(b200ep_ctx* ctx, int H, int K, int x_kind);
  *   deepep_ht.py:143,225-227) and rank_prefix[world+1] (rows
  *   [rank_prefix[s], rank_prefix[s+1]) of recv_x come from rank s). */
 int b200ep_ht_notify(b200ep_ctx* ctx, int slot, const int32_t* dev_tokens_per_rank,
-                     const int32_t* dev_tokens_per_expert, int E, int phases, void* stream);
+                     const int32_t* dev_tokens_per_expert, int T, int E, int phases, void* stream);
 int b200ep_ht_notify_wait(b200ep_ctx* ctx, int slot, int* num_recv_tokens, int32_t* per_expert,
                           int32_t* rank_prefix, int timeout_ms);
 

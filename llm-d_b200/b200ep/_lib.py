@@ -61,12 +61,13 @@ SIGNATURES = {
     "b200ep_set_peer_ptrs": (_i, [_p, C.POINTER(_p), _i]),
     "b200ep_sym_base": (_i, [_p, C.POINTER(_p), C.POINTER(_sz)]),
     "b200ep_peer_base": (_i, [_p, _i, C.POINTER(_p)]),
+    "b200ep_debug_trace": (_i, [_p, _p]),
     "b200ep_set_num_sms": (_i, [_p, _i]),
     "b200ep_layout": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "b200ep_layout_noalloc": (_i, [_i, _p, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "b200ep_quant_fp8": (_i, [_p, _p, _p, _i, _i, _i, _p]),
     "b200ep_ht_capacity": (_i, [_p, _i, _i, _i]),
-    "b200ep_ht_notify": (_i, [_p, _i, _p, _p, _i, _i, _p]),
+    "b200ep_ht_notify": (_i, [_p, _i, _p, _p, _i, _i, _i, _p]),
     "b200ep_ht_notify_wait": (_i, [_p, _i, C.POINTER(_i), _p, _p, _i]),
     "b200ep_ht_dispatch": (_i, [_p, _i, _p, _p, _i, _i, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "b200ep_ht_dispatch_all": (_i, [_p, _i, _p, _p, _i, _i, _p, _i, _p, _p, _p, _p, _p, _i, _i, _i, _i, C.POINTER(_i), _p,

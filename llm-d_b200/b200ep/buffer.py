@@ -226,7 +226,7 @@ class Buffer:
     def ht_notify(self, slot: int, layout: Layout, phases: int = L.PHASE_ALL):
         L.check(
             self.lib.b200ep_ht_notify(self.ctx, slot, _ptr(layout.tokens_per_rank), _ptr(layout.tokens_per_expert),
-                                      layout.num_experts, phases, _stream()),
+                                      int(layout.is_token_in_rank.shape[0]), layout.num_experts, phases, _stream()),
             "ht_notify",
         )
 

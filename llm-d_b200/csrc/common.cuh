@@ -23,18 +23,29 @@ constexpr int kGroup = 128;  // FP8 quantisation group (DEEPEP_QUANT_BLOCK_SIZE,
 
 // ---- symmetric control block (first kCtrlBytes of every rank's region; peers write it)
 constexpr int kCombChunks = 8;     // the overlapped combine signals completion per chunk of source tokens
-constexpr int kCombChunkTokens = 512;
+// Chunk c of a source rank with T tokens = tokens [comb_chunk_begin(T, c), comb_chunk_begin(T, c + 1)): about a
+// sixth each, then smaller, so that what is left to reduce after the LAST flag is 1/32 of the tokens (the
+// reduction of the early chunks runs under the transfer; the last one is pure tail).
+__host__ __device__ inline int comb_chunk_begin(int T, int c) {
+  const int frac32[kCombChunks + 1] = {0, 5, 10, 15, 20, 24, 28, 31, 32};
+  if (c >= kCombChunks) return T;
+  return (int)(((long long)T * frac32[c] / 32) / 32 * 32);  // multiple of 32 tokens
+}
 enum FlagCat { kFlagHtNotify = 0, kFlagHtData, kFlagHtComb, kFlagLlCount, kFlagLlData, kFlagLlComb, kFlagHtCombChunk0,
                kNumFlagCat = kFlagHtCombChunk0 + kCombChunks };
 constexpr size_t kFlagStride = 128;  // one flag per 128-byte line
 constexpr size_t kCtrlFlagsOff = 0;
 constexpr size_t kCtrlFlagsBytes = (size_t)kNumFlagCat * kNumSlots * kMaxRanks * kFlagStride;
-constexpr size_t kCtrlHtCntRankOff = 65536;  // int32 [slot][src][kMaxRanks]
-constexpr size_t kCtrlHtCntExpOff = 81920;   // int32 [slot][src][kMaxLocalExperts]
-constexpr size_t kCtrlLlCntOff = kCtrlHtCntExpOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 4;
+// counts travel as self-validating 8-byte words (call tag << 32 | count): no flag, no system fence
+constexpr size_t kCtrlHtTokOff = 32768;      // u64 [slot][src]: tokens of the source rank in this call
+constexpr size_t kCtrlHtCntRankOff = 65536;  // u64 [slot][src][kMaxRanks]
+constexpr size_t kCtrlHtCntExpOff = 81920;   // u64 [slot][src][kMaxLocalExperts]
+constexpr size_t kCtrlLlCntOff = kCtrlHtCntExpOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 8;
 constexpr size_t kCtrlBytes = 1 << 20;
-static_assert(kCtrlFlagsBytes <= kCtrlHtCntRankOff, "flags overflow");
-static_assert(kCtrlLlCntOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 4 <= kCtrlBytes, "ctrl overflow");
+static_assert(kCtrlFlagsBytes <= kCtrlHtTokOff, "flags overflow");
+static_assert(kCtrlHtCntRankOff + (size_t)kNumSlots * kMaxRanks * kMaxRanks * 8 <= kCtrlHtCntExpOff, "rank counts overflow");
+// low-latency counts: u64 [slot][src][kMaxLocalExperts] words (call tag << 32 | count), each word valid by itself
+static_assert(kCtrlLlCntOff % 8 == 0 && kCtrlLlCntOff + (size_t)kNumSlots * kMaxRanks * kMaxLocalExperts * 8 <= kCtrlBytes, "ctrl overflow");
 
 __host__ __device__ inline size_t flag_off(int cat, int slot, int src) {
   return kCtrlFlagsOff + (((size_t)cat * kNumSlots + slot) * kMaxRanks + src) * kFlagStride;
@@ -47,6 +58,7 @@ struct HtMeta {
   int32_t num_recv;
   int32_t pad[5];
   int32_t send_count[kMaxRanks];       // tokens I send to rank d
+  int32_t src_tokens[kMaxRanks];       // tokens rank s holds in this call (its chunk boundaries follow from it)
   int32_t recv_per_expert[kMaxLocalExperts];
 };
 
@@ -93,6 +105,11 @@ __device__ __forceinline__ void st_release_sys_u64(uint64_t* p, uint64_t v) {
 __device__ __forceinline__ void st_relaxed_sys_u64(uint64_t* p, uint64_t v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+__device__ __forceinline__ uint64_t ld_relaxed_sys_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ unsigned atom_add_acq_rel_gpu(unsigned* p, unsigned v) {
   unsigned r;
@@ -131,6 +148,11 @@ __device__ __forceinline__ void st_na_v4(void* p, const int4& v) {
 // early.  Both are no-ops in a normally launched kernel.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // TMA bulk copy shared -> global (local or peer), tracked by the thread's bulk async-group.
@@ -191,6 +213,23 @@ __device__ __forceinline__ void wait_flag_sys(const uint64_t* flag, uint64_t wan
       __trap();
     }
     __nanosleep(20);
+  }
+}
+
+// A word another GPU writes as (tag << 32 | value) in ONE 8-byte store needs no flag and no fence: spin until the
+// tag is the expected one, the value comes with it.  Traps instead of hanging forever.
+__device__ __forceinline__ int wait_tagged_word(const uint64_t* word, unsigned tag, int what, int me, int peer) {
+  uint64_t v = ld_relaxed_sys_u64(word);
+  if ((unsigned)(v >> 32) == tag) return (int)(uint32_t)v;
+  const long long t0 = clock64();
+  for (;;) {
+    v = ld_relaxed_sys_u64(word);
+    if ((unsigned)(v >> 32) == tag) return (int)(uint32_t)v;
+    if (clock64() - t0 > 60000000000LL) {
+      printf("b200ep: rank %d timed out waiting for a count word (kind %d) from rank %d (want tag %u, have %llu)\n", me, what,
+             peer, tag, (unsigned long long)v);
+      __trap();
+    }
   }
 }
 
@@ -411,6 +450,7 @@ struct LocalScratch {
   unsigned long long layout_epoch;                           // calls completed so far (tags layout_pub)
   unsigned long long layout_pub[kMaxLayoutBlocks][kMaxRanks]; // (epoch << 32 | count) per block and rank
   int layout_hist[kMaxExperts];                              // per-expert totals of the running call, zero between calls
+  unsigned long long trace[128];                             // B200EP_TRACE=1: %globaltimer stamps of the last kernels (b200ep_debug_trace)
   HtMeta ht[kNumSlots];
   unsigned long long epoch[kNumFlagCat][kNumSlots];          // call epochs, advanced on the device
 };

@@ -40,25 +40,24 @@ namespace b200ep {
 
 // ------------------------------------------------------------------ notify (phase-by-phase callers)
 __global__ void __launch_bounds__(256)
-    ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, const int32_t* __restrict__ tok_per_rank,
+    ht_notify_send_kernel(Peers peers, int W, int me, int slot, int e_local, int T, const int32_t* __restrict__ tok_per_rank,
                           const int32_t* __restrict__ tok_per_expert, unsigned long long* epoch_ptr) {
-  notify_publish(peers, W, me, slot, e_local, tok_per_rank, tok_per_expert, epoch_ptr);
+  notify_publish(peers, W, me, slot, e_local, T, tok_per_rank, tok_per_expert, epoch_ptr);
 }
 
 __global__ void __launch_bounds__(256)
     ht_notify_recv_kernel(const char* my_base, int W, int me, int slot, int e_local, HtMeta* meta, HostMirror* host,
                           const unsigned long long* epoch_ptr) {
-  cta_wait_all_sources(my_base, W, kFlagHtNotify, slot, me, epoch_ptr);
-  notify_finish(ctrl_cnt_rank(my_base, slot), kMaxRanks, ctrl_cnt_expert(my_base, slot), kMaxLocalExperts, W, me, slot,
-                e_local, meta, host, *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr));
+  notify_finish(const_cast<char*>(my_base), W, me, slot, e_local, meta, host,
+                *reinterpret_cast<const volatile unsigned long long*>(epoch_ptr));
 }
 
 // world == 1: the whole count "exchange" in one small kernel.
 __global__ void __launch_bounds__(256)
     ht_notify_local_kernel(const int32_t* __restrict__ tok_per_rank, const int32_t* __restrict__ tok_per_expert, int slot,
-                           int e_local, HtMeta* meta, HostMirror* host, unsigned long long* epoch_ptr) {
+                           int e_local, int T, HtMeta* meta, HostMirror* host, unsigned long long* epoch_ptr) {
   const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
-  notify_finish<false>(tok_per_rank, 1, tok_per_expert, e_local, 1, 0, slot, e_local, meta, host, epoch);
+  notify_finish_local(tok_per_rank, tok_per_expert, slot, e_local, T, meta, host, epoch);
   __syncthreads();
   if (threadIdx.x == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = epoch;
 }
@@ -81,6 +80,7 @@ struct HtDispatchArgs {
   const unsigned long long* notify_epoch_ptr;     // count flags (prologue)
   int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
   int prologue;   // 1: wait for the peers' counts and derive the offsets here (no notify-recv launch)
+  unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
 };
 
 // What travels with a row besides its payload, as ONE record of plan.side_bytes (16-byte multiple), identical
@@ -172,24 +172,27 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
   const char* my_base = a.peers.base[a.me];
   int n = 0;  // rows this team has staged so far: stage = n % nstage, one bulk group per row and lane
 
+  const bool trace = a.trace != nullptr && blockIdx.x == 0 && tid == 0;
+  auto stamp = [&](int i) { if (trace) a.trace[i] = globaltimer_ns(); };
+  stamp(20);
   pdl_wait();  // launched early behind the layout kernel (b200ep_ht_dispatch_all): its outputs are needed from here on
+  stamp(21);
   if (a.prologue) {
     // the peers' counts of THIS call (their layout kernels published them; ours did too, which is
     // what advanced *notify_epoch_ptr): wait, then every CTA derives its own send offsets
-    cta_wait_all_sources(my_base, W, kFlagHtNotify, a.slot, a.me, a.notify_epoch_ptr);
-    const int32_t* cr = ctrl_cnt_rank(my_base, a.slot);
-    if (tid < W) {
+    const unsigned long long nep = *reinterpret_cast<const volatile unsigned long long*>(a.notify_epoch_ptr);
+    if (tid < W) {  // lane d: rows the lower ranks send to rank d come before mine (waits word by word, no flag)
       int b = 0;
-      for (int s = 0; s < a.me; ++s) b += __ldcg(&cr[s * kMaxRanks + tid]);
+      for (int s = 0; s < a.me; ++s) b += notify_rank_count(const_cast<char*>(my_base), a.slot, s, tid, (unsigned)nep, a.me);
       s_send_base[tid] = b;
     }
     if (blockIdx.x == 0)  // receive-side bookkeeping and the host mirror (the host may be waiting for it)
-      notify_finish(cr, kMaxRanks, ctrl_cnt_expert(my_base, a.slot), kMaxLocalExperts, W, a.me, a.slot, a.e_local, a.meta,
-                    a.host, *reinterpret_cast<const volatile unsigned long long*>(a.notify_epoch_ptr));
+      notify_finish(const_cast<char*>(my_base), W, a.me, a.slot, a.e_local, a.meta, a.host, nep);
   } else if (tid < W) {
     s_send_base[tid] = a.meta->send_base[tid];
   }
   __syncthreads();
+  stamp(22);
 
   for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
     // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
@@ -263,8 +266,11 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
       bulk_commit();  // every lane, every row (possibly empty): group count == rows staged
     }
   }
+  stamp(23);
   if ((ttid >> 5) == 0) bulk_wait_all();
+  stamp(24);
   if (W > 1) cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtData, a.slot, a.me);  // a single rank has nobody to tell
+  stamp(25);
 }
 
 // ---- world == 1, quantising kind: rows never leave the GPU, so there is nothing to stage.
@@ -398,7 +404,9 @@ struct HtCombineArgs {
   unsigned long long* epoch_ptr;
   unsigned* chunk_done;  // [kCombChunks] private counters of the overlapped kernel
   unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished
+  unsigned* piece_next;  // [kCombChunks] next DMA piece of each chunk (pieces are handed out from a queue)
   int T, W, me, slot;
+  unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
   int rows_per_piece;    // rows one DMA piece moves (<= stage size)
   unsigned stage_bytes;  // bytes of one DMA stage
 };
@@ -414,14 +422,17 @@ __device__ __forceinline__ size_t stage_row_off(const HtPlan& p, int d, int pos,
 // kDmaStages stages; loads run kDmaAhead pieces ahead of stores; a stage is loaded again only after the
 // store that last used it has finished READING it (cp.async.bulk.wait_group.read): when load g is issued
 // at least g - kDmaAhead stores are committed, so "at most kDmaStages - kDmaAhead - 1 pending" covers store g - kDmaStages.
-constexpr int kDmaStages = 4;
-constexpr int kDmaAhead = 2;
+constexpr int kDmaStages = 3;
+constexpr int kDmaAhead = 1;
 // After every store the driver waits until at most kDmaPending of its groups are still incomplete: with 2-row
 // pieces that is > 100 KB per SM on the wire (the fabric needs ~25 KB per SM), so it never starves the link, and
 // it makes "piece number stores - kDmaPending and everything older has LANDED" known at every step -- which is
 // what the per-chunk flags of the overlapped combine need.  (Waiting only at chunk boundaries, down to two
 // pending groups, drained the pipeline eight times per call: 470 us against 410 us for the push alone at EP=8.)
-constexpr int kDmaPending = 4;
+// The queue must stay SHALLOW: 600-680 GB/s x ~3 us of latency is ~2 MB for the whole GPU, i.e. one 14 KB row per
+// SM.  With 4 pending groups of 2-row pieces per driver, 25 MB (of 58 MB at EP=2) sat in the fabric's queues: chunk 0
+// was issued by 16 us but had landed only at 50 us, every flag came late and the reduction could not hide.
+constexpr int kDmaPending = 2;
 struct DmaPipe {
   char* stage;
   uint64_t* bar;
@@ -448,8 +459,8 @@ __device__ __forceinline__ void dma_store(DmaPipe& p) {
 // pieces known to have landed (all of this thread's stores older than the kDmaPending most recent ones)
 __device__ __forceinline__ int dma_landed(const DmaPipe& p) { return p.stores - kDmaPending; }
 
-// Row ranges of chunk c (source tokens [c*512, (c+1)*512), the last chunk takes the rest) inside every
-// remote source's block of this rank's receive order: s_lo[k][c] for source (me+1+k) % W.
+// Row ranges of chunk c (comb_chunk_begin of the SOURCE's token count) inside every remote source's block
+// of this rank's receive order: s_lo[k][c] for source (me+1+k) % W.
 __device__ __forceinline__ void combine_chunk_bounds(const HtCombineArgs& a, const int32_t* src_idx,
                                                      int (*s_lo)[kCombChunks + 1]) {
   const int W = a.W, tid = threadIdx.x;
@@ -460,7 +471,7 @@ __device__ __forceinline__ void combine_chunk_bounds(const HtCombineArgs& a, con
     if (c == kCombChunks) {
       lo = hi;
     } else {
-      const int want = c * kCombChunkTokens;
+      const int want = comb_chunk_begin(a.meta->src_tokens[s], c);
       while (lo < hi) {
         const int mid = (lo + hi) >> 1;
         if (__ldcg(src_idx + mid) < want) lo = mid + 1; else hi = mid;
@@ -470,26 +481,28 @@ __device__ __forceinline__ void combine_chunk_bounds(const HtCombineArgs& a, con
   }
 }
 
-// The driver thread's part of chunk c for CTA `cta` of `nctas`: pieces interleave the remote sources
-// starting at rank me+1, so that at any moment the W ranks push along a permutation (all ranks
-// converging on rank 0 first was measured 2.2x slower).  Returns the number of pieces stored.
+// The driver thread's part of chunk c: pieces interleave the remote sources starting at rank me+1, so that
+// at any moment the W ranks push along a permutation (all ranks converging on rank 0 first was measured 2.2x
+// slower).  Pieces come from a queue (one atomic per piece): the SMs do not get the same share of the fabric,
+// and with a static split the slowest driver decided when every chunk -- and the whole push -- was complete
+// (trace at EP=2: CTA 0 done at 73 us, the kernel's last piece at ~105 us).  Returns the number of pieces stored.
 template <typename AfterStore>
 __device__ __forceinline__ int combine_push_chunk(const HtCombineArgs& a, DmaPipe& p, int (*s_lo)[kCombChunks + 1], int c,
-                                                  int cta, int nctas, AfterStore after_store) {
+                                                  AfterStore after_store) {
   const int W = a.W, R = a.rows_per_piece, row_bytes = 2 * a.plan.H;
   int maxp = 0;
   for (int k = 0; k < W - 1; ++k) maxp = max(maxp, (s_lo[k][c + 1] - s_lo[k][c] + R - 1) / R);
   const long long total = (long long)maxp * (W - 1);
-  long long i = cta;
   int loaded = 0, stored = 0;
   bool more = true;
   for (;;) {
     if (more && loaded - stored < kDmaAhead) {
-      // next valid piece of this CTA
+      // next valid piece from the queue
       bool found = false;
-      while (i < total) {
+      for (;;) {
+        const long long i = (long long)atomicAdd(&a.piece_next[c], 1u);
+        if (i >= total) break;
         const int k = (int)(i % (W - 1)), j = (int)(i / (W - 1));
-        i += nctas;
         const int lo = s_lo[k][c] + j * R, hi = min(s_lo[k][c + 1], lo + R);
         if (lo >= hi) continue;
         const int s = (a.me + 1 + k) % W;
@@ -532,8 +545,11 @@ __global__ void __launch_bounds__(128, 1) ht_combine_send_kernel(const __grid_co
     p.bar = s_bar;
     p.stage_bytes = a.stage_bytes;
     p.loads = p.stores = 0;
-    for (int c = 0; c < kCombChunks; ++c) combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x, []() {});
+    for (int c = 0; c < kCombChunks; ++c) combine_push_chunk(a, p, s_lo, c, []() {});
     bulk_wait_all();
+    // the last driver to leave the queues rewinds them for the next call
+    if (atom_add_acq_rel_gpu(&a.piece_next[kCombChunks], 1u) == gridDim.x - 1)
+      for (int c = 0; c <= kCombChunks; ++c) a.piece_next[c] = 0;
   }
   cta_done_then_signal(a.done, a.epoch_ptr, a.peers, a.W, kFlagHtComb, a.slot, a.me);
 }
@@ -558,10 +574,11 @@ __device__ __forceinline__ int4 pack8_bf16(const float (&acc)[8]) {
 // resolved once, then the warp walks the range in batches of kRedVec vectors per lane with the loads
 // of up to four source rows in flight together.  kMaxSrc = ranks the code is built for.
 constexpr int kRedVec = 4;
+// where the rows of token t are: lane d resolves rank d's row (its own rows straight from y, the others from the
+// stage), everybody gets all pointers; dmask = ranks that hold a row of this token
 template <int kMaxSrc>
-__device__ __forceinline__ void reduce_item(const HtCombineArgs& a, const char* stage, int my_first, int t, int vbeg,
-                                            int vend, int lane) {
-  constexpr int kGrp = kMaxSrc < 4 ? kMaxSrc : 4;
+__device__ __forceinline__ unsigned reduce_resolve(const HtCombineArgs& a, const char* stage, int my_first, int t, int lane,
+                                                   const char* (&rows)[kMaxSrc]) {
   const int W = a.W, row_bytes = 2 * a.plan.H;
   const char* rowp = nullptr;
   if (lane < W && a.in_rank[(size_t)t * W + lane]) {
@@ -570,10 +587,16 @@ __device__ __forceinline__ void reduce_item(const HtCombineArgs& a, const char* 
                         : stage + ((size_t)lane * a.plan.t_cap + pos) * row_bytes;
   }
   const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
-  const char* rows[kMaxSrc];
 #pragma unroll
   for (int d = 0; d < kMaxSrc; ++d)
     rows[d] = reinterpret_cast<const char*>(__shfl_sync(0xffffffffu, (unsigned long long)rowp, d));
+  return dmask;
+}
+template <int kMaxSrc>
+__device__ __forceinline__ void reduce_accumulate(const HtCombineArgs& a, const char* const (&rows)[kMaxSrc], unsigned dmask,
+                                                  int t, int vbeg, int vend, int lane) {
+  constexpr int kGrp = kMaxSrc < 4 ? kMaxSrc : 4;
+  const int row_bytes = 2 * a.plan.H;
   int4* dst = reinterpret_cast<int4*>(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes);
   for (int v0 = vbeg; v0 < vend; v0 += 32 * kRedVec) {
     float acc[kRedVec][8];
@@ -612,6 +635,13 @@ __device__ __forceinline__ void reduce_item(const HtCombineArgs& a, const char* 
       if (v < vend) st_na_v4(dst + v, pack8_bf16(acc[j]));
     }
   }
+}
+template <int kMaxSrc>
+__device__ __forceinline__ void reduce_item(const HtCombineArgs& a, const char* stage, int my_first, int t, int vbeg,
+                                            int vend, int lane) {
+  const char* rows[kMaxSrc];
+  const unsigned dmask = reduce_resolve<kMaxSrc>(a, stage, my_first, t, lane, rows);
+  reduce_accumulate<kMaxSrc>(a, rows, dmask, t, vbeg, vend, lane);
 }
 
 // Phase RECV on its own: wait for every peer's push, then reduce (static partition of the items).
@@ -704,12 +734,16 @@ __global__ void __launch_bounds__(512, 1) ht_combine_fused_kernel(const __grid_c
   const int W = a.W;
   const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(a.epoch_ptr) + 1;
   const int32_t* src_idx = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
+  const bool trace = a.trace != nullptr && blockIdx.x == 0;
+  auto stamp = [&](int i) { if (trace) a.trace[i] = globaltimer_ns(); };
+  if (tid == 0) stamp(30);
   combine_chunk_bounds(a, src_idx, s_lo);
   if (tid == 0) {
     for (int i = 0; i < kDmaStages; ++i) mbar_init(&s_bar[i], 1);
     fence_mbar_init();
   }
   __syncthreads();
+  if (tid == 0) stamp(31);
 
   if (tid == 0) {
     // ------------------------------------------------ push (DMA driver)
@@ -722,55 +756,70 @@ __global__ void __launch_bounds__(512, 1) ht_combine_fused_kernel(const __grid_c
       const unsigned prev = atom_add_acq_rel_gpu(&a.chunk_done[c], 1u);
       if (prev == gridDim.x - 1) {
         a.chunk_done[c] = 0;
+        if (a.trace) a.trace[70 + c] = globaltimer_ns();
         fence_acq_rel_sys();
         for (int d = 0; d < W; ++d)
           if (d != a.me)
             st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagHtCombChunk0 + c, a.slot, a.me)), want);
+        if (a.trace) a.trace[80 + c] = globaltimer_ns();
       }
     };
     int end_seq[kCombChunks];  // stores issued by the end of chunk c: chunk c has landed once dma_landed() >= end_seq[c]
     int next_arrive = 0;
     for (int c = 0; c < kCombChunks; ++c) {
-      combine_push_chunk(a, p, s_lo, c, blockIdx.x, gridDim.x, [&]() {
+      combine_push_chunk(a, p, s_lo, c, [&]() {
         while (next_arrive < c && end_seq[next_arrive] <= dma_landed(p)) arrive(next_arrive++);
       });
       end_seq[c] = p.stores;
+      stamp(40 + c);
     }
     bulk_wait_all();
     while (next_arrive < kCombChunks) arrive(next_arrive++);
+    stamp(32);
   }
   __syncwarp();
 
-  // ------------------------------------------------ reduce (every warp; warp 0 arrives late)
-  const int nvec = 2 * a.plan.H / 16;
-  const int nsplit = nvec >= 256 ? 2 : 1;
-  const int per = (nvec / nsplit + 31) / 32 * 32;
-  const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
-  const int my_first = a.meta->rank_prefix[a.me];
-  for (int c = 0; c < kCombChunks; ++c) {
-    const int t0 = c * kCombChunkTokens;
-    const int t1 = c == kCombChunks - 1 ? a.T : min(a.T, t0 + kCombChunkTokens);
-    if (lane < W && lane != a.me)
-      wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagHtCombChunk0 + c, a.slot, lane)), want,
-                    kFlagHtCombChunk0 + c, a.me, lane);
-    __syncwarp();
-    if (t1 <= t0) continue;
-    const int items = (t1 - t0) * nsplit;
-    for (;;) {
-      int it = 0;
-      if (lane == 0) it = (int)atomicAdd(&a.red_next[c], 1u);
-      it = __shfl_sync(0xffffffffu, it, 0);
-      if (it >= items) break;
-      const int t = t0 + it / nsplit, vbeg = (it % nsplit) * per;
-      reduce_item<kMaxRanks>(a, stage, my_first, t, vbeg, min(nvec, vbeg + per), lane);
+  // ------------------------------------------------ reduce (warps 1..15 of every CTA; warp 0 only drives the DMA)
+  // An item = (token, 2 KB piece of its row): one batch of loads per source row, so an item costs about one
+  // memory round trip.  Items of a chunk are split statically over the reducer warps of the grid, and a warp
+  // resolves the row pointers of its first item BEFORE it waits for the chunk's flags: what is left on the
+  // critical path after the last flag is one round trip and the stores.  (With half rows handed out from a
+  // queue an item took ~5 us -- atomic, index loads, 3.5 batches -- and the last chunk ~10 us.)
+  if (warp > 0) {
+    const int nvec = 2 * a.plan.H / 16;
+    const int per = 32 * kRedVec;
+    const int nsplit = (nvec + per - 1) / per;
+    const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
+    const int my_first = a.meta->rank_prefix[a.me];
+    const int nred = gridDim.x * ((blockDim.x >> 5) - 1), w_g = blockIdx.x * ((blockDim.x >> 5) - 1) + warp - 1;
+    for (int c = 0; c < kCombChunks; ++c) {
+      const int t0 = comb_chunk_begin(a.T, c), t1 = comb_chunk_begin(a.T, c + 1);
+      const int items = (t1 - t0) * nsplit;
+      int it = w_g;
+      const char* rows[kMaxRanks];
+      unsigned dmask = 0;
+      if (it < items) dmask = reduce_resolve<kMaxRanks>(a, stage, my_first, t0 + it / nsplit, lane, rows);
+      if (lane < W && lane != a.me)
+        wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagHtCombChunk0 + c, a.slot, lane)), want,
+                      kFlagHtCombChunk0 + c, a.me, lane);
+      __syncwarp();
+      if (warp == 1 && lane == 0) stamp(50 + c);
+      while (it < items) {
+        const int vbeg = (it % nsplit) * per;
+        reduce_accumulate<kMaxRanks>(a, rows, dmask, t0 + it / nsplit, vbeg, min(nvec, vbeg + per), lane);
+        it += nred;
+        if (it < items) dmask = reduce_resolve<kMaxRanks>(a, stage, my_first, t0 + it / nsplit, lane, rows);
+      }
+      if (warp == 1 && lane == 0) stamp(60 + c);
     }
   }
-  // the last warp of the whole grid to run out of work rewinds the queues and advances the epoch
-  // (every warp has read the old epoch by then)
+  // the last warp of the whole grid to finish rewinds the queues and advances the epoch (every warp has read the
+  // old epoch by then)
   if (lane == 0) {
     const unsigned prev = atom_add_acq_rel_gpu(&a.red_next[kCombChunks], 1u);
     if (prev == gridDim.x * (blockDim.x >> 5) - 1) {
-      for (int c = 0; c <= kCombChunks; ++c) a.red_next[c] = 0;
+      a.red_next[kCombChunks] = 0;
+      for (int c = 0; c <= kCombChunks; ++c) a.piece_next[c] = 0;
       *reinterpret_cast<volatile unsigned long long*>(a.epoch_ptr) = want;
     }
   }
@@ -808,7 +857,7 @@ static int check_slot(b200ep_ctx* c, int slot, const char* who) {
 }
 
 extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_tokens_per_rank,
-                                const int32_t* dev_tokens_per_expert, int E, int phases, void* stream) {
+                                const int32_t* dev_tokens_per_expert, int T, int E, int phases, void* stream) {
   int rc = check_slot(c, slot, "ht_notify");
   if (rc) return rc;
   if (E <= 0 || E % c->world || E / c->world > kMaxLocalExperts) {
@@ -826,7 +875,7 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
       }
       ++c->epoch[kFlagHtNotify][slot];
       c->ht_e_local[slot] = el;
-      ht_notify_local_kernel<<<1, 256, 0, st>>>(dev_tokens_per_rank, dev_tokens_per_expert, slot, el, &c->local->ht[slot],
+      ht_notify_local_kernel<<<1, 256, 0, st>>>(dev_tokens_per_rank, dev_tokens_per_expert, slot, el, T, &c->local->ht[slot],
                                                c->host_dev, &c->local->epoch[kFlagHtNotify][slot]);
       B200EP_CUDA(cudaGetLastError());
     }
@@ -839,7 +888,7 @@ extern "C" int b200ep_ht_notify(b200ep_ctx* c, int slot, const int32_t* dev_toke
     }
     ++c->epoch[kFlagHtNotify][slot];  // host mirror of the device epoch, for b200ep_ht_notify_wait
     c->ht_e_local[slot] = el;
-    ht_notify_send_kernel<<<1, 256, 0, st>>>(c->peers, c->world, c->rank, slot, el, dev_tokens_per_rank,
+    ht_notify_send_kernel<<<1, 256, 0, st>>>(c->peers, c->world, c->rank, slot, el, T, dev_tokens_per_rank,
                                              dev_tokens_per_expert, &c->local->epoch[kFlagHtNotify][slot]);
     B200EP_CUDA(cudaGetLastError());
   }
@@ -925,6 +974,8 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
     a.prologue = (prologue && c->world > 1) ? 1 : 0;
+    static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
+    a.trace = trace_env ? c->local->trace : nullptr;
     // called from b200ep_ht_dispatch_all the layout kernel is queued right in front: start early behind it
     static const int pdl_env = getenv("B200EP_PDL") ? atoi(getenv("B200EP_PDL")) : 1;
     const bool pdl = prologue && pdl_env;
@@ -1058,15 +1109,18 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.me = c->rank;
   a.slot = slot;
   a.epoch_ptr = &c->local->epoch[kFlagHtComb][slot];
+  static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
+  a.trace = trace_env ? c->local->trace : nullptr;
   a.chunk_done = &c->local->done[16 + slot * kCombChunks];
   a.red_next = &c->local->done[32 + slot * 16];
+  a.piece_next = &c->local->done[72 + slot * 16];
   const int row_bytes = 2 * H;
-  // DMA pieces: as many whole rows as fit 29 KB (two DeepSeek rows; the probe gives 672 GB/s for 28 KB pieces and
-  // 677 GB/s for 42 KB ones at EP=8, and smaller pieces make the per-chunk flags of the overlapped kernel timelier)
-  a.rows_per_piece = 29 * 1024 / row_bytes;
+  // DMA pieces: as many whole rows as fit 15 KB (one DeepSeek row; the probe gives 660-665 GB/s for 14 KB pieces and
+  // 677 GB/s for 42 KB ones at EP=8, but small pieces keep the fabric queue shallow and the chunk flags timely)
+  a.rows_per_piece = 15 * 1024 / row_bytes;
   if (a.rows_per_piece < 1) a.rows_per_piece = 1;
   static const int piece_env = getenv("B200EP_HT_PIECE_ROWS") ? atoi(getenv("B200EP_HT_PIECE_ROWS")) : 0;
-  if (piece_env > 0 && piece_env < a.rows_per_piece) a.rows_per_piece = piece_env;
+  if (piece_env > 0 && (size_t)piece_env * row_bytes * kDmaStages <= 200 * 1024) a.rows_per_piece = piece_env;
   a.stage_bytes = (unsigned)a.rows_per_piece * (unsigned)row_bytes;
   const size_t dma_smem = (size_t)kDmaStages * a.stage_bytes;
   const bool any = phases & (B200EP_PHASE_SEND | B200EP_PHASE_RECV);

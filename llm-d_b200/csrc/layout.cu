@@ -197,11 +197,11 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
   if (tail.mode == kTailLocal) {
     const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) + 1;
-    notify_finish<false>(s_base, 1, s_hist, e_local, 1, 0, tail.slot, e_local, tail.meta, tail.host, epoch);
+    notify_finish_local(s_base, s_hist, tail.slot, e_local, T, tail.meta, tail.host, epoch);
     __syncthreads();
     if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(tail.epoch_ptr) = epoch;
   } else if (tail.mode == kTailPublish) {
-    notify_publish(tail.peers, W, tail.me, tail.slot, e_local, s_base, s_hist, tail.epoch_ptr);
+    notify_publish(tail.peers, W, tail.me, tail.slot, e_local, T, s_base, s_hist, tail.epoch_ptr);
   }
 }
 

@@ -23,6 +23,8 @@
 // Combine: owners push occupied result rows back into stage[token][k] on the source
 // (same staging + bulk copy); the source does sum_k w_k * y_k in fp32 (multiply, then
 // add, k ascending) and writes bf16 once.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200ep {
@@ -38,6 +40,15 @@ struct LlScratch {  // private, per slot
   int32_t layout_range[kMaxLocalExperts * kMaxRanks * 2];
 };
 static_assert(sizeof(LlScratch) * kNumSlots <= (4u << 20), "ll scratch");
+
+// Per-expert counts travel as self-validating words (call tag << 32 | count), one 8-byte store per (expert, peer):
+// the receiver polls the words it needs, so the count exchange costs no system fence and no flag round trip.
+__device__ __forceinline__ uint64_t* ll_count_word(char* base, int slot, int src, int e) {
+  return reinterpret_cast<uint64_t*>(base + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + src) * kLlMaxExperts + e;
+}
+__device__ __forceinline__ uint64_t ll_count_pack(unsigned long long tag, int n) {
+  return ((tag & 0xffffffffull) << 32) | (uint32_t)n;
+}
 
 // Positions and counts from per-expert token bit masks: every (token, k) entry ORs its token's bit
 // into mask[e] (shared-memory atomics -- the resulting mask does not depend on arrival order), then
@@ -66,14 +77,15 @@ __global__ void __launch_bounds__(1024)
       sc->pos[i] = p;
     }
   }
+  const unsigned long long tag = *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) + 1;
   for (int e = tid; e < E; e += blockDim.x) {
     int n = 0;
     for (int w = 0; w < nw; ++w) n += __popc(s_mask[e * nw + w]);
     sc->cnt_mine[e] = n;
-    for (int d = 0; d < W; ++d)
-      (reinterpret_cast<int32_t*>(peers.base[d] + kCtrlLlCntOff) + ((size_t)slot * kMaxRanks + me) * kLlMaxExperts)[e] = n;
+    for (int d = 0; d < W; ++d) st_relaxed_sys_u64(ll_count_word(peers.base[d], slot, me, e), ll_count_pack(tag, n));
   }
-  single_cta_signal(epoch_ptr, peers, W, kFlagLlCount, slot, me);
+  __syncthreads();
+  if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(epoch_ptr) = tag;
 }
 
 struct LlDispatchArgs {
@@ -86,6 +98,7 @@ struct LlDispatchArgs {
   size_t slot_off;
   unsigned long long *epoch_cnt_ptr, *epoch_data_ptr;
   int T, W, me, slot, E, ue8m0, ids_i64, fused, wait_data;
+  unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
 };
 
 // fused == 1: the kernel also does the COUNT phase (production path, one launch for count + send):
@@ -109,7 +122,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
   float* s_scale = reinterpret_cast<float*>(s_mem + row_bytes);
   const bool packed = kFp8 && a.ue8m0 == 2;
   const char* my_base = a.peers.base[a.me];
-  const int32_t* cnt = reinterpret_cast<const int32_t*>(my_base + kCtrlLlCntOff) + (size_t)a.slot * kMaxRanks * kLlMaxExperts;
+  char* my_base_w = a.peers.base[a.me];
   auto load_id = [&](int t, int k) -> long long {
     return a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + k]
                      : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + k];
@@ -118,6 +131,11 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
   // never keep it off the GPU), blocks 1.. are token CTAs
   const int ntok_ctas = a.fused ? (int)gridDim.x - 1 : (int)gridDim.x;
   const int tok_cta = a.fused ? (int)blockIdx.x - 1 : (int)blockIdx.x;
+  const bool trace = a.trace != nullptr && tid == 0;
+  auto stamp = [&](int i) { if (trace) a.trace[i] = globaltimer_ns(); };
+  bool st_q = false, st_i = false;
+  if (blockIdx.x == 0) stamp(0);
+  if (tok_cta == 0) stamp(2);
 
   if (a.fused && blockIdx.x == 0) {
     // ---------------- count role (one CTA): per-expert histogram -> every peer, count flags
@@ -129,17 +147,18 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
       if (v >= 0 && v < a.E) atomicAdd(&s_cnt[(int)v], 1);
     }
     __syncthreads();
-    for (int e = tid; e < a.E; e += blockDim.x) {
-      const int n = s_cnt[e];
-      for (int d = 0; d < W; ++d)
-        (reinterpret_cast<int32_t*>(a.peers.base[d] + kCtrlLlCntOff) + ((size_t)a.slot * kMaxRanks + a.me) * kLlMaxExperts)[e] = n;
+    const unsigned long long tag = *reinterpret_cast<volatile unsigned long long*>(a.epoch_cnt_ptr) + 1;
+    for (int i = tid; i < a.E * W; i += blockDim.x) {  // every (expert, peer) word: one 8-byte store each, no fence, no flag
+      const int e = i / W, d = i % W;
+      st_relaxed_sys_u64(ll_count_word(a.peers.base[d], a.slot, a.me, e), ll_count_pack(tag, s_cnt[e]));
     }
-    single_cta_signal(a.epoch_cnt_ptr, a.peers, W, kFlagLlCount, a.slot, a.me);
+    __syncthreads();
+    if (tid == 0) *reinterpret_cast<volatile unsigned long long*>(a.epoch_cnt_ptr) = tag;
+    stamp(1);
   } else {
     // count flags of this call carry (data epoch before this kernel) + 1: both advance once per dispatch,
     // and the data epoch cannot move before every CTA of this kernel is past its waits
-    const unsigned long long want_cnt =
-        a.fused ? *reinterpret_cast<const volatile unsigned long long*>(a.epoch_data_ptr) + 1 : 0ull;
+    const unsigned want_cnt = (unsigned)(*reinterpret_cast<const volatile unsigned long long*>(a.epoch_data_ptr) + 1);
     bool counts_ready = false;
     for (int t = tok_cta; t < a.T || !counts_ready; t += ntok_ctas) {
       const bool have_token = t < a.T;
@@ -189,21 +208,14 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
         }
         fence_proxy_async_smem();
       }
+      if (tok_cta == 0 && !st_q) { stamp(3); st_q = true; }
       if (!counts_ready) {
-        if (a.fused) {
-          if (tid < W)
-            wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(kFlagLlCount, a.slot, tid)), want_cnt,
-                          kFlagLlCount, a.me, tid);
-          __syncthreads();
-        } else {
-          cta_wait_all_sources(my_base, W, kFlagLlCount, a.slot, a.me, a.epoch_cnt_ptr);
-        }
         counts_ready = true;
-        if (tok_cta == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges
+        if (tok_cta == 0) {  // receive-side bookkeeping of this rank: counts and per-source ranges (waits word by word)
           for (int el = tid; el < e_local; el += blockDim.x) {
             int p = 0;
             for (int s = 0; s < W; ++s) {
-              const int n = __ldcg(&cnt[(size_t)s * kLlMaxExperts + a.me * e_local + el]);
+              const int n = wait_tagged_word(ll_count_word(my_base_w, a.slot, s, a.me * e_local + el), want_cnt, kFlagLlCount, a.me, s);
               a.sc->layout_range[(el * W + s) * 2] = p;
               a.sc->layout_range[(el * W + s) * 2 + 1] = n;
               p += n;
@@ -218,8 +230,8 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
         int slot_idx = -1;
         if (id >= 0 && id < a.E) {
           const int e = (int)id, d = e / e_local, el = e % e_local;
-          int base = 0;
-          for (int s = 0; s < a.me; ++s) base += __ldcg(&cnt[(size_t)s * kLlMaxExperts + e]);
+          int base = 0;  // rows of lower ranks come first: wait for exactly the count words this entry needs
+          for (int s = 0; s < a.me; ++s) base += wait_tagged_word(ll_count_word(my_base_w, a.slot, s, e), want_cnt, kFlagLlCount, a.me, s);
           slot_idx = base + (a.fused ? s_pos[tid] : a.sc->pos[t * K + tid]);
           if (slot_idx < cap) {
             char* dst = a.peers.base[d] + a.slot_off;
@@ -243,6 +255,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
           s_dst[tid] = slot_idx >= 0 ? (int)(id / e_local) : 0;
         }
       }
+      if (tok_cta == 0 && !st_i) { stamp(4); st_i = true; }
       if (kFp8 && packed && have_token) {
         // Packed UE8M0 scales (what DeepGEMM reads on sm_100, vLLM fp8_utils.py:643-714): the scales are
         // powers of two, so only the biased exponent byte travels, four groups per int32, written straight
@@ -261,6 +274,7 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
       }
     }
     if (tid < K) bulk_wait_all();
+    if (tok_cta == 0) stamp(5);
   }
   // every CTA (count role included): completion counter, last one raises the data flags
   __syncthreads();
@@ -269,14 +283,17 @@ __global__ void __launch_bounds__(256) ll_dispatch_send_kernel(const __grid_cons
     if (prev == gridDim.x - 1) {
       *a.done = 0;
       const uint64_t epoch = *reinterpret_cast<volatile unsigned long long*>(a.epoch_data_ptr) + 1;
+      stamp(6);
       fence_acq_rel_sys();
       for (int d = 0; d < W; ++d)
         st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagLlData, a.slot, a.me)), epoch);
       *reinterpret_cast<volatile unsigned long long*>(a.epoch_data_ptr) = epoch;
+      stamp(7);
       if (a.wait_data)
         for (int s = 0; s < W; ++s)
           wait_flag_sys(reinterpret_cast<const uint64_t*>(my_base + flag_off(kFlagLlData, a.slot, s)), epoch, kFlagLlData,
                         a.me, s);
+      stamp(8);
     }
   }
 }
@@ -294,6 +311,7 @@ struct LlCombineArgs {
   size_t slot_off;
   unsigned long long* epoch_ptr;
   int T, W, me, slot, E, ids_i64, fused;
+  unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
 };
 
 __device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a);
@@ -305,13 +323,21 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
   // the epoch this call publishes; the stored epoch only advances after every warp of the grid has read it
   const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(a.epoch_ptr) + 1;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  const int W = a.W, K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
-  const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
+  const bool trace = a.trace != nullptr && threadIdx.x == 0;
+  auto stamp = [&](int i) { if (trace) a.trace[i] = globaltimer_ns(); };
+  if (blockIdx.x == 0) stamp(10);
+  const int W = a.W, cap = a.plan.cap, e_local = a.plan.e_local;
+  const int row_bytes = 2 * a.plan.H;
   char* s_row = s_mem + (size_t)warp * row_bytes;
-  (void)K;
   const int32_t* src_info = reinterpret_cast<const int32_t*>(a.peers.base[a.me] + a.slot_off + a.plan.off_src);
   // Occupied rows only: exclusive prefix of recv_count over the local experts (one warp, shared memory).
   __shared__ int s_pref[kMaxLocalExperts + 1];
+  __shared__ __align__(8) uint64_t s_bar[16];  // one mbarrier per warp (TMA loads of its stage)
+  unsigned uses = 0;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 16; ++i) mbar_init(&s_bar[i], 1);
+    fence_mbar_init();
+  }
   if (warp == 0) {
     const int per = (e_local + 31) / 32;
     int sum = 0;
@@ -357,34 +383,23 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
     int s = 0;
     while (s + 1 < W && sl >= a.sc->layout_range[(el * W + s + 1) * 2]) ++s;
     if (s == a.me) continue;  // the reduce reads local rows straight from dev_y
-    const int flat = __ldcg(src_info + idx);  // t*K + k on the source rank
-    bulk_wait_read0();
-    __syncwarp();
-    const int4* src = reinterpret_cast<const int4*>(reinterpret_cast<const char*>(a.y) + (size_t)idx * row_bytes);
-    constexpr int U = 4;
-    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
-      int4 raw[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
-        if (v < nvec) raw[u] = ld_nc_v4(src + v);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int v = v0 + u * 32 + lane;
-        if (v < nvec) reinterpret_cast<int4*>(s_row)[v] = raw[u];
-      }
-    }
-    fence_proxy_async_smem();
-    __syncwarp();
+    // the row never touches registers: TMA load (global -> this warp's stage), then TMA store (stage -> peer)
     if (lane == 0) {
+      const int flat = __ldcg(src_info + idx);  // t*K + k on the source rank
+      bulk_wait_read0();                        // the previous store has finished reading the stage
+      mbar_expect_tx(&s_bar[warp], row_bytes);
+      bulk_g2s(s_row, reinterpret_cast<const char*>(a.y) + (size_t)idx * row_bytes, row_bytes, &s_bar[warp]);
+      mbar_wait(&s_bar[warp], uses & 1u);
+      ++uses;
       bulk_s2g(a.peers.base[s] + a.slot_off + a.plan.off_stage + (size_t)flat * row_bytes, s_row, row_bytes);
       bulk_commit();
     }
       }
     }
   }
+  if (blockIdx.x == 0) stamp(11);
   bulk_wait_all();
+  if (blockIdx.x == 0) stamp(12);
   // all rows this CTA took have landed: add them to the completion count; the CTA that completes the
   // last row publishes (one system fence); the last CTA of the grid rewinds the queue for the next call
   __syncthreads();
@@ -397,6 +412,7 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
       fence_acq_rel_sys();
       for (int d = 0; d < W; ++d)
         st_relaxed_sys_u64(reinterpret_cast<uint64_t*>(a.peers.base[d] + flag_off(kFlagLlComb, a.slot, a.me)), want);
+      stamp(15);
     }
     if (fin == gridDim.x - 1) {
       // every CTA of the grid is past the queue (so each has read the old epoch): rewind the queue
@@ -412,7 +428,9 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
       wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagLlComb, a.slot, threadIdx.x)), want,
                     kFlagLlComb, a.me, threadIdx.x);
     __syncthreads();
+    if (blockIdx.x == 0) stamp(13);
     ll_reduce_items(a);
+    if (blockIdx.x == 0) stamp(14);
   }
 }
 
@@ -572,6 +590,8 @@ extern "C" int b200ep_ll_dispatch(b200ep_ctx* c, int slot, const void* dev_x_bf1
     a.ids_i64 = ids_i64;
     a.fused = fused ? 1 : 0;
     a.wait_data = wait_in_kernel ? 1 : 0;
+    static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
+    a.trace = trace_env ? c->local->trace : nullptr;
     size_t smem = (size_t)(plan.row_bytes + plan.scale_bytes + 127) / 128 * 128;
     if (fused && smem < (size_t)E * 4) smem = (size_t)E * 4;  // the count CTA's histogram
     const int grid = ll_grid(c, T) + (fused ? 1 : 0);
@@ -642,6 +662,8 @@ extern "C" int b200ep_ll_combine(b200ep_ctx* c, int slot, const void* dev_y, con
   a.ids_i64 = ids_i64;
   a.epoch_ptr = &c->local->epoch[kFlagLlComb][slot];
   a.fused = (phases == B200EP_PHASE_ALL) ? 1 : 0;
+  static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
+  a.trace = trace_env ? c->local->trace : nullptr;
   const int row_bytes = 2 * H;
   if (phases & B200EP_PHASE_SEND) {
     if (!dev_y) {

@@ -308,6 +308,16 @@ int b200ep_peer_base(b200ep_ctx* c, int rank, void** dev_base) {
   return B200EP_OK;
 }
 
+int b200ep_debug_trace(b200ep_ctx* c, unsigned long long* out128) {
+  if (!c || !out128) {
+    set_error("debug_trace: bad argument");
+    return B200EP_ERR_ARG;
+  }
+  B200EP_CUDA(cudaSetDevice(c->device));
+  B200EP_CUDA(cudaMemcpy(out128, c->local->trace, sizeof(c->local->trace), cudaMemcpyDeviceToHost));
+  return B200EP_OK;
+}
+
 int b200ep_set_num_sms(b200ep_ctx* c, int num_sms) {
   if (!c || num_sms < 0) {
     set_error("set_num_sms: bad argument");
