@@ -1003,8 +1003,12 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
       B200EP_CUDA(cudaGetLastError());
     } else {
       const size_t stage_bytes = (size_t)(plan.row_bytes + plan.side_bytes + 127) / 128 * 128;
-      const int ctas_per_sm = x_kind == B200EP_X_BF16_QUANT ? 3 : 2;
-      a.nstage = 2 * kTeams * stage_bytes * ctas_per_sm <= 216 * 1024 ? 2 : 1;  // every resident CTA must still fit
+      static const int ctas_env = getenv("B200EP_HT_DISPATCH_CTAS") ? atoi(getenv("B200EP_HT_DISPATCH_CTAS")) : 0;
+      const int max_ctas = x_kind == B200EP_X_BF16_QUANT ? 3 : 2;
+      const int ctas_per_sm = (ctas_env > 0 && ctas_env < max_ctas) ? ctas_env : max_ctas;
+      a.nstage = 2 * kTeams * stage_bytes * max_ctas <= 216 * 1024 ? 2 : 1;  // every resident CTA must still fit
+      static const int nstage_env = getenv("B200EP_HT_DISPATCH_STAGES") ? atoi(getenv("B200EP_HT_DISPATCH_STAGES")) : 0;
+      if (nstage_env == 1) a.nstage = 1;
       const size_t smem = (size_t)kTeams * a.nstage * stage_bytes;
       if (smem > 220 * 1024) {
         set_error("ht_dispatch: a row of %d bytes does not fit the shared-memory stage", plan.row_bytes);

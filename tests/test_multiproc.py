@@ -60,3 +60,21 @@ def test_gpu_ipc_world_baseline_shapes(world):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-6000:]
     for k in range(world):
         assert f"GPU-MP-FULL-OK rank {k}/{world}" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("backend", ["deepep_high_throughput", "deepep_low_latency"])
+@pytest.mark.parametrize("world", [2, 8])
+def test_gpu_vllm_managers_world(world, backend):
+    """vLLM builds its own DeepEP all2all manager for the llm-d backend names at data_parallel_size = world, the manager's
+    handle is the b200ep shim, and vLLM's own prepare/finalize classes give oracle-exact results on it with two
+    micro-batches in flight (tests/mp_vllm_worker.py)."""
+    import torch
+
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    pytest.importorskip("vllm")
+    r = _torchrun(world, [os.path.join(ROOT, "tests", "mp_vllm_worker.py"), backend], 29691 + world, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-8000:]
+    for k in range(world):
+        assert f"VLLM-MGR-OK {backend} rank {k}/{world}" in r.stdout
