@@ -12,7 +12,7 @@ Printed JSON (one line, rank 0):
   value      whole-job tokens/s, inputs resident in HBM, CUDA-event timed, max over ranks
   e2e        same metric through the public API with HOST buffers: pinned->device copies of the
              step's inputs and a device->host read of the combined output inside the timed region
-             (the expert stand-in between dispatch and combine -- a dequantise -- is also inside)
+             (double-buffered on copy streams; expert outputs are resident bf16 rows)
   roofline   dominant kernel vs measured HBM peak (N=1) or NVLink per-direction peak (N>1)
   cpu_baseline  the reference's CPU dispatch/combine (oracle/cpu_reference.py, a port of vLLM
              cpu_fused_moe_torch) timed on this box's host cores on a bounded sample (N=1 only)
@@ -40,6 +40,7 @@ T, H, E, K = 4096, 7168, 256, 8
 LL_T = 128
 NVLINK_PEAK_GBS = 770.0  # measured peer-copy GB/s per direction on this pool (B200_PROFILING.md); nominal 900
 METRIC = "dispatch+combine tokens/s"
+DTYPE = "bf16 in, fp8 e4m3 + fp32 scales dispatched, bf16 combined with fp32 accumulate"
 WORKLOAD = "synthetic DeepSeek-V3 MoE layer (hidden 7168, 256 experts, top-8), 4096 tokens/rank bf16->FP8 high-throughput dispatch+combine"
 
 
@@ -131,10 +132,11 @@ def cpu_baseline(sample_tokens: int, repeats: int, threads: int | None = None):
     torch.set_num_threads(n)
     x, ids, w = make_inputs(1234, sample_tokens)
     ids32 = ids.to(torch.int32)
-    cpu_dispatch_combine(x, w, ids32, E)  # warm-up
+    cpu_quant_fp8(x); cpu_dispatch_combine(x, w, ids32, E)  # warm-up
     best, times = None, []
     for _ in range(repeats):
         t0 = time.perf_counter()
+        cpu_quant_fp8(x)
         cpu_dispatch_combine(x, w, ids32, E)
         dt = time.perf_counter() - t0
         times.append(dt)
@@ -144,36 +146,87 @@ def cpu_baseline(sample_tokens: int, repeats: int, threads: int | None = None):
         "unit": "tokens/s",
         "cores": torch.get_num_threads(),
         "kind": "port",
-        "sample": f"{sample_tokens} tokens x hidden {H}, top-{K} of {E} experts, bf16, identity experts, "
+        "sample": f"{sample_tokens} tokens x hidden {H}, top-{K} of {E} experts, bf16 -> FP8-128 quantise, identity experts, "
                   f"best of {repeats} (mean {sum(times) / len(times):.3f} s/step); "
                   "port of vLLM cpu_fused_moe_torch (cpu_fused_moe.py:444-449,467-481)",
     }, best
 
 
+NBUF = 4  # rotating input sets, so that a timed step never finds its inputs in the 126 MB L2
+
+
+def _config(world: int):
+    """The `config` object: identical in the b200ep arm and in the reference arm (the driver compares them)."""
+    return {"workload": WORKLOAD, "ep_size": world, "tokens_per_rank": T, "hidden": H, "experts": E, "topk": K,
+            "l2": f"GPU arm: {NBUF} rotating input sets ({NBUF * (T * H * 2) >> 20} MiB of x) > 126 MB L2; host arm: not applicable"}
+
+
+def _profile_json(name):
+    """Numbers that come from committed profiler output (profiles/), never literals in this file."""
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def cpu_quant_fp8(x: torch.Tensor):
+    """The reference's CPU form of per_token_group_quant_fp8 (vLLM fp8_utils.py:510-591, group 128): what its
+    high-throughput path runs before the dispatch (deepep_ht.py:282-289), in torch on the host cores."""
+    g = x.float().view(x.shape[0], -1, 128)
+    s = g.abs().amax(dim=2).clamp_(min=1e-10) / 448.0
+    q = (g / s.unsqueeze(-1)).clamp_(-448.0, 448.0).to(torch.float8_e4m3fn)
+    return q.view(x.shape[0], -1), s
+
+
 def run_reference(args):
+    """The reference's own CPU implementation of the path (oracle/cpu_reference.py, a port of vLLM's
+    cpu_fused_moe_torch: the reference repo holds no source for it), all host threads.  One step = the SAME
+    workload as a b200ep step at this N: N ranks' worth of 4096 tokens (the CPU has no ranks: the expert-parallel
+    exchange degenerates to the gather/scatter over all N*4096 tokens), bf16 in, FP8-128 quantise, dispatch,
+    identity experts, fp32 weighted combine."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     steps, warm = max(1, args.steps), max(0, args.warmup)
     from oracle.cpu_reference import cpu_dispatch_combine
 
+    world = max(1, args.gpus)
     torch.set_num_threads(os.cpu_count() or 1)
-    sample = 4096
-    x, ids, w = make_inputs(1234, sample)
-    ids32 = ids.to(torch.int32)
+    parts = [make_inputs(1234 + r) for r in range(world)]
+    x = torch.cat([p[0] for p in parts]); ids32 = torch.cat([p[1] for p in parts]).to(torch.int32)
+    w = torch.cat([p[2] for p in parts])
+    tokens = x.shape[0]
+
+    def step(stable=False):
+        nonlocal x, ids32, w
+        cpu_quant_fp8(x)  # the payload the reference dispatches is FP8; the CPU fragment itself moves bf16 rows
+        return cpu_dispatch_combine(x, w, ids32, E, stable=stable)
+
+    # bounded: if K steps of the full workload would take more than ~2.5 minutes on these cores, a step becomes a
+    # proportionally smaller sample of it (tokens/s is what is reported either way)
+    p0 = time.perf_counter(); step(); probe = time.perf_counter() - p0
+    if probe * (steps + warm) > 150.0:
+        keep = max(256, int(tokens * 150.0 / (probe * (steps + warm))) // 256 * 256)
+        x, ids32, w = x[:keep].contiguous(), ids32[:keep].contiguous(), w[:keep].contiguous()
+        tokens = keep
     for _ in range(warm):
-        cpu_dispatch_combine(x, w, ids32, E)
+        step()
     t0 = time.perf_counter()
     for _ in range(steps):
-        cpu_dispatch_combine(x, w, ids32, E)
+        step()
     dt = (time.perf_counter() - t0) / steps
-    val = sample / dt
+    t1 = time.perf_counter(); step(stable=True); dt_stable = time.perf_counter() - t1
+    t2 = time.perf_counter(); cpu_quant_fp8(x); dt_quant = time.perf_counter() - t2
+    val = tokens / dt
     base = {"value": val, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{sample} tokens/step x {steps} steps, hidden {H}, top-{K} of {E}, bf16, identity experts"}
+            "sample": f"{tokens} of {world * T} tokens/step x {steps} steps, hidden {H}, top-{K} of {E}, bf16 -> FP8-128 quantise + dispatch + "
+                      f"identity experts + fp32 combine; of which quantise {dt_quant * 1e3:.0f} ms; the stable-argsort variant "
+                      f"takes {dt_stable * 1e3:.0f} ms/step"}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "bf16 (fp32 reduce)", "data": "synthetic", "config": {"workload": WORKLOAD, "ep_size": 1, "host": "cpu"},
+        "dtype": DTYPE, "data": "synthetic", "config": _config(world),
         "cpu_baseline": base, "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
     return 0
@@ -347,6 +400,10 @@ def main():
     import b200ep
     from b200ep import _lib as L
 
+    # libraries (NCCL's version banner) write to stdout; the contract is ONE JSON line there: everything else goes to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -384,11 +441,10 @@ def main():
         except parity.ParityError as ex:
             print(f"[rank {rank}] PARITY FAILED: {ex}", file=sys.stderr, flush=True)
             if rank == 0:
-                print(json.dumps({"metric": METRIC, "value": None, "n_gpus": world, "parity": {"error": str(ex)[:2000]}}))
+                os.write(real_stdout, (json.dumps({"metric": METRIC, "value": None, "n_gpus": world, "parity": {"error": str(ex)[:2000]}}) + "\n").encode())
             os._exit(3)
         barrier()
 
-    NBUF = 4  # rotate inputs so a step never finds its inputs in the 126 MB L2
     xs, idss, wss = [], [], []
     for b in range(NBUF):
         x, ids, w = make_inputs(1000 * b + rank)
@@ -522,7 +578,14 @@ def main():
     else:
         r = sum(remote_copies) / len(remote_copies)  # remote copies actually made per step by this rank's peers -> me
         db, cb = r * (H + 4 * H // 128), r * 2 * H
-        peak, bound, unit_note = NVLINK_PEAK_GBS, "nvlink", "measured peer-copy GB/s per direction (guide); 900 nominal"
+        probe = _profile_json("r02_fabric_probe.json") or {}
+        if str(world) in probe.get("best_push_gbs", {}):
+            peak = float(probe["best_push_gbs"][str(world)])
+            unit_note = (f"best SM-driven push between the symmetric regions measured on this pool at EP={world} with every rank "
+                         "pushing at once (bench.py --impl probe, profiles/r02_fabric_probe.json); 900 nominal, 770 one-directional peer copy")
+        else:
+            peak, unit_note = NVLINK_PEAK_GBS, "measured peer-copy GB/s per direction (guide); 900 nominal"
+        bound = "nvlink"
     # roofline durations: the kernels that move the algorithmic bytes.  N>1: the push kernels (their
     # duration does not include waiting for peers); N=1: dispatch send kernel and the reduce kernel.
     st = torch.tensor([ds_avg, cs_avg], device=dev)
@@ -532,16 +595,19 @@ def main():
     d_k, c_k = (ds_max, cs_max) if world > 1 else (ds_avg, c_avg)
     d_gbs, c_gbs = db / (d_k * 1e-3) / 1e9, cb / (c_k * 1e-3) / 1e9
     if world > 1:
-        dominant = "ht_combine_send_kernel (bf16 push)" if c_k >= d_k else "ht_dispatch_send_kernel"
+        dominant = "ht_combine_send_kernel (bf16 rows, TMA load -> TMA store to the peer)" if c_k >= d_k else "ht_dispatch_send_kernel (fused quantise + TMA fan-out)"
     else:
-        dominant = "ht_combine_recv_kernel (fp32 reduce)" if c_k >= d_k else "ht_dispatch_send_kernel (fused quantise)"
+        dominant = "ht_combine_local_kernel (gather, fp32 accumulate)" if c_k >= d_k else "ht_dispatch_local_kernel (fused quantise)"
     dom_gbs = c_gbs if c_k >= d_k else d_gbs
+    ncu = _profile_json("r02_ncu_n1.json") if world == 1 else None
+    traffic = None
+    if ncu:
+        traffic = ncu.get("combine_dram_bytes") if c_k >= d_k else ncu.get("dispatch_dram_bytes")
     roofline = {
         "bound": bound, "achieved": dom_gbs, "peak": peak, "unit": "GB/s", "frac": dom_gbs / peak,
-        # dram__bytes_read+write per launch from the ncu --set full capture of round 1 (profiles/r01_ncu_full_n1.txt),
-        # N=1 only: reduce kernel 58.8 MB read + 9.9 MB written (the rest of the 58.7 MB output is still in L2),
-        # dispatch kernel 59.2 + 4.2 MB
-        "traffic": (None if world > 1 else (68.68e6 if c_k >= d_k else 63.40e6)),
+        # dram__bytes_read + dram__bytes_write per launch of that kernel, read from the committed summary of the
+        # ncu --set full capture (profiles/r02_ncu_n1.json, made by tools/ncu_summary.py); null when there is none
+        "traffic": traffic,
         "kernel": dominant, "peak_source": unit_note,
         "how": "CUDA events around each kernel, launches queued back to back, L2 flushed (512 MB read) before each; "
                "N>1: push kernels only (max over ranks), N=1: dispatch send kernel and reduce kernel",
@@ -554,32 +620,59 @@ def main():
         "step_frac": (db + cb) / (ms_step * 1e-3) / 1e9 / peak,
     }
 
-    # ---- end to end through the public API with host buffers
+    # ---- end to end through the public API with host buffers: every step copies ITS inputs from pinned host memory
+    # and ITS combined output back, all inside the timed region; the copies run on streams of their own with two
+    # buffer sets, so step i+1's inputs travel while step i computes and step i-1's output returns (PCIe is full
+    # duplex).  Expert outputs are resident bf16 rows, as in the device-timed step (the GEMMs are out of scope).
     hx = [x.cpu().pin_memory() for x in xs[:2]]
     hi = [i.cpu().pin_memory() for i in idss[:2]]
     hw = [w.cpu().pin_memory() for w in wss[:2]]
-    hout = torch.empty(T, H, dtype=torch.bfloat16).pin_memory()
-    dx, di, dw = torch.empty_like(xs[0]), torch.empty_like(idss[0]), torch.empty_like(wss[0])
+    houts = [torch.empty(T, H, dtype=torch.bfloat16).pin_memory() for _ in range(2)]
+    dxs = [torch.empty_like(xs[0]) for _ in range(2)]
+    dis = [torch.empty_like(idss[0]) for _ in range(2)]
+    dws = [torch.empty_like(wss[0]) for _ in range(2)]
+    douts = [torch.empty(T, H, dtype=torch.bfloat16, device=dev) for _ in range(2)]
+    s_in, s_out, s_main = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev), torch.cuda.current_stream()
+    ev_in = [torch.cuda.Event() for _ in range(2)]
+    ev_comp = [torch.cuda.Event() for _ in range(2)]
+    ev_out = [torch.cuda.Event() for _ in range(2)]
+    for e in ev_comp + ev_out:
+        e.record(s_main)
+
+    def e2e_h2d(i):
+        b = i % 2
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_comp[b])  # the step that last used this input set has finished with it
+            dxs[b].copy_(hx[b], non_blocking=True); dis[b].copy_(hi[b], non_blocking=True); dws[b].copy_(hw[b], non_blocking=True)
+            ev_in[b].record(s_in)
 
     def e2e_step(i):
         b = i % 2
-        dx.copy_(hx[b], non_blocking=True); di.copy_(hi[b], non_blocking=True); dw.copy_(hw[b], non_blocking=True)
-        rx, rs, ridx, rw, per_expert, h = buf.dispatch(dx, di, dw, E, quantize=True)
-        M = h.num_recv
-        y = (rx.float().view(M, H // 128, 128) * rs[:, :, None]).view(M, H).to(torch.bfloat16)  # expert stand-in
-        buf.combine(y, h, out)
-        hout.copy_(out, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        s_main.wait_event(ev_in[b])
+        s_main.wait_event(ev_out[b])  # this output buffer's previous copy to the host is done
+        rx, rs, ridx, rw, per_expert, h = buf.dispatch(dxs[b], dis[b], dws[b], E, quantize=True)
+        buf.combine(y_pool[: h.num_recv], h, douts[b])
+        ev_comp[b].record(s_main)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_comp[b])
+            houts[b].copy_(douts[b], non_blocking=True)
+            ev_out[b].record(s_out)
 
-    e2e_steps = max(3, min(steps, 10))
-    for i in range(3):
-        e2e_step(i)
+    def e2e_run(n):
+        e2e_h2d(0)
+        for i in range(n):
+            if i + 1 < n:
+                e2e_h2d(i + 1)
+            e2e_step(i)
+        torch.cuda.synchronize()
+
+    e2e_steps = max(4, min(steps, 20))
+    e2e_run(4)
     barrier()
     t0 = time.perf_counter()
     s0, s1 = ev(), ev()
     s0.record()
-    for i in range(e2e_steps):
-        e2e_step(i)
+    e2e_run(e2e_steps)
     s1.record()
     torch.cuda.synchronize()
     e_ms = torch.tensor([s0.elapsed_time(s1)], device=dev)
@@ -589,8 +682,10 @@ def main():
     e2e_wall = time.perf_counter() - t0
     e2e = {
         "value": world * T * e2e_steps / (float(e_ms.item()) / 1e3), "unit": "tokens/s",
-        "h2d_bytes_per_step": dx.numel() * 2 + di.numel() * 8 + dw.numel() * 4, "d2h_bytes_per_step": out.numel() * 2,
-        "ms_per_step": float(e_ms.item()) / e2e_steps, "wall_s": e2e_wall,
+        "h2d_bytes_per_step": dxs[0].numel() * 2 + dis[0].numel() * 8 + dws[0].numel() * 4, "d2h_bytes_per_step": douts[0].numel() * 2,
+        "ms_per_step": float(e_ms.item()) / e2e_steps, "wall_s": e2e_wall, "steps": e2e_steps,
+        "how": "Buffer.dispatch + Buffer.combine from pinned host buffers; H2D of the step's x/ids/weights and D2H of its output "
+               "inside the timed region, double-buffered on copy streams; per-rank copies, aggregate tokens/s",
     }
 
     # ---- low-latency decode mode: CUDA-graph replay
@@ -609,16 +704,14 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": steps, "warmup": warm,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 in, fp8 e4m3 + fp32 scales dispatched, bf16 combined with fp32 accumulate",
-            "data": "synthetic",
-            "config": {"workload": WORKLOAD, "ep_size": world, "tokens_per_rank": T, "hidden": H, "experts": E, "topk": K,
-                       "l2": f"{NBUF} rotating input sets ({NBUF * (T * H * 2) >> 20} MiB of x) > 126 MB L2",
-                       "tokens_per_s_per_gpu": value / world},
+            "dtype": DTYPE, "data": "synthetic", "config": _config(world), "tokens_per_s_per_gpu": value / world,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
-            "gpu_launches": steps * (4 if world == 1 else 6) + R * (2 if world == 1 else 4), "ll": ll,
+            # kernels of libb200ep.so inside the timed region: per step layout + dispatch + combine (EP=1), plus the
+            # receive-side unpack kernel at EP>1
+            "gpu_launches": steps * (3 if world == 1 else 4), "ll": ll,
             "host_sync_free": nosync, "parity": parity_res,
         }
-        print(json.dumps(line))
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     buf.destroy()
     if world > 1:
         dist.destroy_process_group()

@@ -86,7 +86,50 @@ def get_classes():
                                           expert_num_tokens_per_expert_list, expert_topk_weights, None, quant_config,
                                           defer_input_quant=False)
 
-    _classes = {"B200EPHTPrepareAndFinalize": B200EPHTPrepareAndFinalize}
+    class B200EPHTNoSyncPrepareAndFinalize(B200EPHTPrepareAndFinalize):
+        """Host-sync-free high-throughput prepare: the dispatch never waits on the host, the
+        received tensors have a fixed worst-case number of rows (``max_tokens_per_rank * num_dispatchers``) and the
+        per-expert counts stay on the device, so ``ExpertTokensMetadata.expert_num_tokens_cpu`` is None -- the form
+        vLLM's experts already accept from the low-latency path (deepep_ll.py:328-342) and the reason it has to turn
+        CUDA graphs off for ``deepep_high_throughput`` today (config/compilation.py:1189-1205, deepep_ht.py:222-227).
+        Rows beyond the received count hold stale data with expert id -1 / weight 0 semantics: their top-k ids are
+        set to the out-of-rank sentinel, so experts that honour expert_map skip them."""
+
+        def __init__(self, *args, max_tokens_per_rank: int, **kwargs):
+            super().__init__(*args, **kwargs)
+            self.max_tokens_per_rank_ = int(max_tokens_per_rank)
+
+        def _do_dispatch_fused(self, tokens, rank_topk_ids, rank_topk_weights, num_experts, quant_config) -> Callable:
+            assert tokens.shape[0] <= self.max_tokens_per_rank_, "more tokens than the worst case this object was built for"
+            previous_event = dbo_get_previous_event(self.buffer.capture)
+            dbo_yield_and_switch_from_compute_to_comm()
+            worst = self.max_tokens_per_rank_ * self.num_dispatchers_
+            (token_data, expert_topk_ids, expert_topk_weights, _, handle, event) = self.buffer.dispatch(
+                x=tokens, handle=None, num_tokens_per_rank=None, num_tokens_per_rdma_rank=None, is_token_in_rank=None,
+                num_tokens_per_expert=torch.empty(num_experts, dtype=torch.int32, device="meta"), topk_idx=rank_topk_ids,
+                topk_weights=rank_topk_weights, expert_alignment=1, num_worst_tokens=worst,
+                config=self._get_dispatch_config(), previous_event=previous_event,
+                async_finish=self.async_prepare and not dbo_enabled(), allocate_on_comm_stream=False,
+                b200ep_quantize=True, b200ep_ue8m0=_ue8m0_wanted())
+            self.handles[dbo_current_ubatch_id()] = handle
+            dbo_switch_to_compute_sync()
+
+            def receiver():
+                if event.event is not None:
+                    event.current_stream_wait()
+                expert_x, expert_x_scale = token_data
+                rows = torch.arange(worst, device=expert_x.device)
+                live = (rows < handle.num_recv_dev).unsqueeze(1)
+                sentinel = num_experts - 1 if self.rank_expert_offset == 0 else 0
+                ids = torch.where(live & (expert_topk_ids != -1), expert_topk_ids + self.rank_expert_offset, sentinel)
+                weights = torch.where(live, expert_topk_weights, 0.0)
+                meta = mk.ExpertTokensMetadata(expert_num_tokens=handle.recv_per_expert_dev, expert_num_tokens_cpu=None)
+                return expert_x, expert_x_scale, meta, ids, weights
+
+            return receiver
+
+    _classes = {"B200EPHTPrepareAndFinalize": B200EPHTPrepareAndFinalize,
+                "B200EPHTNoSyncPrepareAndFinalize": B200EPHTNoSyncPrepareAndFinalize}
     return _classes
 
 

@@ -116,3 +116,46 @@ def test_vllm_deepep_ll_prepare_finalize_on_shim(group):
         assert (out.cpu().float() - ref).abs().max().item() <= 0.08 * ref.abs().max().item()
     finally:
         buf.destroy()
+
+
+def test_host_sync_free_prepare_finalize_on_shim(group):
+    """Route B, f2: B200EPHTNoSyncPrepareAndFinalize never waits on the host; counts come back on the device
+    (expert_num_tokens_cpu is None) and rows beyond the received count are neutralised."""
+    import deep_ep
+    from b200ep.vllm_backend import get_classes
+
+    mkq, _, _, _, NoOP = _vllm_bits()
+    torch.cuda.set_device(0)
+    T, H, E, K, cap = 200, 2048, 64, 8, 256
+    x, ids, w = make_rank_inputs(T, H, E, K, seed=21, mask_frac=0.2)
+    ids[5] = -1  # a token without any expert: fewer rows than tokens
+    buf = deep_ep.Buffer(group=group, num_nvl_bytes=1 << 30, num_rdma_bytes=0, low_latency_mode=False,
+                         num_qps_per_rank=1, explicitly_destroy=True)
+    try:
+        pf = get_classes()["B200EPHTNoSyncPrepareAndFinalize"](buf, num_dispatchers=1, dp_size=1, rank_expert_offset=0,
+                                                              max_tokens_per_rank=cap)
+        qc = mkq(w1_scale=torch.ones(1, device=DEV), w2_scale=torch.ones(1, device=DEV), block_shape=[128, 128])
+        a1q, a1s, meta, oids, ow = pf.prepare(x.to(DEV), w.to(DEV), ids.to(DEV), E, None, False, qc, False)
+        torch.cuda.synchronize()
+        assert meta.expert_num_tokens_cpu is None and a1q.shape == (cap, H)
+        valid = (ids >= 0).any(1).numpy()
+        rows = np.nonzero(valid)[0]
+        M = len(rows)
+        assert np.array_equal(meta.expert_num_tokens.cpu().numpy(), np.bincount(ids.numpy()[ids.numpy() >= 0], minlength=E))
+        got_s = a1s.cpu().numpy()[:M]
+        oq0, os0 = fp8.group_quant_fp8(bf16_bits(x), ue8m0=False)
+        oq1, os1 = fp8.group_quant_fp8(bf16_bits(x), ue8m0=True)
+        oq, osc = (oq0, os0) if np.array_equal(got_s, os0[rows]) else (oq1, os1)
+        assert np.array_equal(got_s, osc[rows]) and np.array_equal(u8(a1q)[:M], oq[rows])
+        want_ids = np.where(ids.numpy()[rows] >= 0, ids.numpy()[rows], E - 1)
+        assert np.array_equal(oids.cpu().numpy()[:M], want_ids)
+        assert (oids.cpu().numpy()[M:] == E - 1).all() and (ow.cpu().numpy()[M:] == 0).all()
+        y = torch.full((cap, H), float("nan"), dtype=torch.bfloat16, device=DEV)
+        y[:M] = torch.randn(M, H, device=DEV).to(torch.bfloat16)
+        out = torch.full((T, H), float("nan"), dtype=torch.bfloat16, device=DEV)
+        pf.finalize(out, y, ow, oids, False, NoOP())
+        torch.cuda.synchronize()
+        assert torch.equal(out[torch.from_numpy(rows).to(DEV)], y[:M])
+        assert bool((out[torch.from_numpy(~valid).to(DEV)] == 0).all())
+    finally:
+        buf.destroy()
