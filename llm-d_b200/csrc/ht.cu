@@ -290,7 +290,7 @@ __device__ __forceinline__ void st_v8(void* p, const uint4& lo, const uint4& hi)
                "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
                : "memory");
 }
-template <int kH, bool kUe8m0, int kLocalU = 2, int kMinCtas = 3>
+template <int kH, bool kUe8m0, int kLocalU = 1, int kMinCtas = 6>
 __global__ void __launch_bounds__(256, kMinCtas) ht_dispatch_local_kernel(const __grid_constant__ HtDispatchArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int H = kH > 0 ? kH : a.plan.H, K = a.plan.K;
@@ -984,22 +984,17 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
       a.nstage = 0;
       // one 64-byte pair per lane and item, 6 CTAs per SM (40 registers): measured 18.4 us at 4096 x 7168 against
       // 20.4 us with two pairs per lane at 3 CTAs per SM -- resident warps matter more than bytes in flight per warp
-      static const int var_env = getenv("B200EP_HT_LOCAL_VAR") ? atoi(getenv("B200EP_HT_LOCAL_VAR")) : 0;
-      const int U = var_env == 1 ? 2 : 1;
+      const int U = 1;
       const int nseg = (H / 32 + 32 * U - 1) / (32 * U);
       const long long items = (long long)T * nseg;
       const int grid = (int)((items + 7) / 8 > 0 ? (items + 7) / 8 : 1);
-#define LOCAL_LAUNCH(HH, UE)                                                                                            \
-  do {                                                                                                                  \
-    if (var_env == 1) B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<HH, UE, 2, 4>, grid, 256, 0, st, pdl, a));     \
-    else B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<HH, UE, 1, 6>, grid, 256, 0, st, pdl, a));                 \
-  } while (0)
       if (H == 7168) {
-        if (ue8m0) LOCAL_LAUNCH(7168, true); else LOCAL_LAUNCH(7168, false);
+        if (ue8m0) B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<7168, true>, grid, 256, 0, st, pdl, a));
+        else B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<7168, false>, grid, 256, 0, st, pdl, a));
       } else {
-        if (ue8m0) LOCAL_LAUNCH(0, true); else LOCAL_LAUNCH(0, false);
+        if (ue8m0) B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<0, true>, grid, 256, 0, st, pdl, a));
+        else B200EP_CUDA(launch_kernel(ht_dispatch_local_kernel<0, false>, grid, 256, 0, st, pdl, a));
       }
-#undef LOCAL_LAUNCH
       B200EP_CUDA(cudaGetLastError());
     } else {
       const size_t stage_bytes = (size_t)(plan.row_bytes + plan.side_bytes + 127) / 128 * 128;
@@ -1139,10 +1134,8 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
         return B200EP_ERR_ARG;
       }
       const int nseg = (H / 16 + 32 * kCombU - 1) / (32 * kCombU);
-      static const int mode_env = getenv("B200EP_HT_LOCAL_MODE") ? atoi(getenv("B200EP_HT_LOCAL_MODE")) : 1;
       const long long items = (long long)T * nseg;
-      if (mode_env == 1) ht_combine_local_kernel<false><<<(int)((items + 7) / 8 > 0 ? (items + 7) / 8 : 1), 256, 0, st>>>(a);
-      else ht_combine_local_kernel<true><<<grid_for(c, items, 8, 3), 256, 0, st>>>(a);
+      ht_combine_local_kernel<false><<<(int)((items + 7) / 8 > 0 ? (items + 7) / 8 : 1), 256, 0, st>>>(a);
       B200EP_CUDA(cudaGetLastError());
     }
     return B200EP_OK;
