@@ -216,6 +216,41 @@ int b200ep_ht_combine(b200ep_ctx* ctx, int slot, const void* dev_y, void* dev_ou
                       const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H,
                       int phases, void* stream);
 
+/* ------------------------------ expert-grouped layout for grouped GEMMs (after an HT dispatch) */
+
+/* Replaces deepgemm_moe_permute -> ep_scatter (vLLM fused_moe/deep_gemm_utils.py:347-420, 56-249; called from
+ * fused_moe/experts/deep_gemm_moe.py:279-291) on the rows the dispatch of `slot` received: every row is copied,
+ * with its scales, to one output row per LOCAL expert in its top-k.  Expert e owns output rows
+ * [start[e], start[e] + count[e]), start = exclusive prefix of the counts rounded up to `alignment`
+ * (compute_aligned_M, deep_gemm_utils.py:26-44; 128 for DeepGEMM's contiguous layout).
+ *   rows_bound        host-side upper bound on the rows received (num_recv_tokens, or the worst case after a
+ *                     host-sync-free dispatch): sizes the grids, the true count is read on the device
+ *   dev_out_x         [m_cap, H] e4m3 (or [m_cap, H] bf16 for B200EP_X_BF16)          out, 32-byte aligned
+ *   dev_out_scales    [m_cap, H/128] fp32, row-major (NULL for B200EP_X_BF16)         out
+ *   dev_expert_ids    [m_cap] int32: expert of every occupied row, -1 in the padding  out ("m_indices")
+ *   dev_inv_perm      [rows_bound, K] int32: output row of entry (m, k), -1 if none   out
+ *   dev_expert_start  [E/world + 1] int32: start[], last = rows the layout needs      out, may be NULL
+ *   m_cap             rows the caller's buffers hold (the kernel traps if the layout needs more)
+ * Rows inside an expert are in received order (source rank, then source token): deterministic, where the
+ * reference uses an atomic counter.  A token's top-k ids must be distinct (top-k routing guarantees it).
+ * Calls on one context must not overlap on the GPU (they share the plan kernel's scratch). */
+int b200ep_ht_permute(b200ep_ctx* ctx, int slot, int alignment, int rows_bound, void* dev_out_x,
+                      float* dev_out_scales, int32_t* dev_expert_ids, int32_t* dev_inv_perm,
+                      int32_t* dev_expert_start, int m_cap, void* stream);
+
+/* Replaces deepgemm_unpermute_and_reduce -> ep_gather (deep_gemm_utils.py:423-440, 252-344; called from
+ * deep_gemm_moe.py:322-329) AND the deep_ep.Buffer.combine that follows it (deepep_ht.py:364-376) in one
+ * operation.  dev_y_grouped is the grouped GEMM output, bf16 [m_cap, H], rows as laid out by b200ep_ht_permute.
+ * SEND: for every received token m the expert rank forms z[m] = bf16( sum_k w[m,k] * y[inv_perm[m,k]] ) over the
+ *       entries with a local expert (fp32 accumulator, one fused multiply-add per entry, k ascending: ep_gather's
+ *       arithmetic) inside the push and sends it to the token's source rank; no [M, H] intermediate is written.
+ * RECV: as b200ep_ht_combine (fp32 sum over the returned rows in rank order, one bf16 rounding).
+ * dev_topk_weights: [rows, K] fp32, or NULL for the weights the dispatch delivered (recv_topk_weights); pass
+ * ones when the router weights were already applied to the input (apply_router_weight_on_input). */
+int b200ep_ht_combine_permuted(b200ep_ctx* ctx, int slot, const void* dev_y_grouped, const int32_t* dev_inv_perm,
+                               const float* dev_topk_weights, void* dev_out, const uint8_t* dev_is_token_in_rank,
+                               const int32_t* dev_send_off, int T, int H, int phases, void* stream);
+
 /* ---------------------------------------------------- low-latency (decode) */
 
 /* Replaces deep_ep.Buffer.get_low_latency_rdma_size_hint (all2all.py:287-292). */

@@ -74,6 +74,8 @@ SIGNATURES = {
                                     _p, _i, _p]),
     "b200ep_ht_views": (_i, [_p, _i, C.POINTER(HtView)]),
     "b200ep_ht_combine": (_i, [_p, _i, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "b200ep_ht_permute": (_i, [_p, _i, _i, _i, _p, _p, _p, _p, _p, _i, _p]),
+    "b200ep_ht_combine_permuted": (_i, [_p, _i, _p, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
     "b200ep_ll_size_hint": (_sz, [_i, _i, _i, _i]),
     "b200ep_ll_dispatch": (_i, [_p, _i, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "b200ep_ll_views": (_i, [_p, _i, C.POINTER(LlView)]),

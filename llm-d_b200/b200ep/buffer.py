@@ -413,6 +413,63 @@ class Buffer:
         )
         return out
 
+    # ------------------------------------------------------------ expert-grouped layout (DeepGEMM contiguous)
+    @staticmethod
+    def aligned_rows(num_rows: int, K: int, local_experts: int, alignment: int = 128, per_expert=None) -> int:
+        """Rows the grouped layout needs: the exact sum of the per-expert counts rounded up to ``alignment`` when
+        the counts are known on the host, else the worst case (vLLM ``compute_aligned_M``,
+        fused_moe/deep_gemm_utils.py:26-44)."""
+        if per_expert is not None:
+            return sum((int(n) + alignment - 1) // alignment * alignment for n in per_expert)
+        m = num_rows * K + local_experts * (alignment - 1)
+        return (m + alignment - 1) // alignment * alignment
+
+    def ht_permute(self, handle: HtHandle, *, alignment: int = 128, per_expert=None, out_x=None, out_scales=None):
+        """Regroup the rows ``handle``'s dispatch received by local expert (vLLM ``deepgemm_moe_permute``,
+        fused_moe/deep_gemm_utils.py:347-420).  Returns (a_perm [M_sum, H], a_scale_perm [M_sum, H/128] or None,
+        expert_ids [M_sum] int32, inv_perm [num_recv, K] int32).  ``per_expert`` (the list the dispatch returned)
+        sizes the outputs exactly; without it (host-sync-free dispatch) they are sized for the worst case."""
+        h = handle
+        el = h.E // self.world
+        dev = self._sym.device
+        m_cap = self.aligned_rows(h.num_recv, h.K, el, alignment, per_expert if per_expert else None)
+        bf16 = h.x_kind == L.X_BF16
+        if out_x is None:
+            out_x = torch.empty((m_cap, h.H), dtype=torch.bfloat16 if bf16 else torch.float8_e4m3fn, device=dev)
+        assert out_x.is_contiguous() and out_x.shape[0] >= m_cap and out_x.shape[1] == h.H
+        if not bf16 and out_scales is None:
+            out_scales = torch.empty((m_cap, h.H // 128), dtype=torch.float32, device=dev)
+        expert_ids = torch.empty(m_cap, dtype=torch.int32, device=dev)
+        inv_perm = torch.empty((h.num_recv, h.K), dtype=torch.int32, device=dev)
+        L.check(
+            self.lib.b200ep_ht_permute(self.ctx, h.slot, alignment, h.num_recv, _ptr(out_x), _ptr(out_scales),
+                                       _ptr(expert_ids), _ptr(inv_perm), None, m_cap, _stream()),
+            "ht_permute",
+        )
+        return out_x[:m_cap], (None if bf16 else out_scales[:m_cap]), expert_ids, inv_perm
+
+    def combine_permuted(self, y_grouped: torch.Tensor, inv_perm: torch.Tensor, handle: HtHandle, out=None, *,
+                         topk_weights: torch.Tensor | None = None, phases: int = L.PHASE_ALL):
+        """``deepgemm_unpermute_and_reduce`` + ``Buffer.combine`` in one operation: the weighted fp32 reduction over a
+        received token's local experts is done inside the push (see b200ep_ht_combine_permuted).
+        y_grouped: bf16 [M_sum, H], rows as laid out by ``ht_permute``."""
+        h = handle
+        assert y_grouped.dtype == torch.bfloat16 and y_grouped.is_contiguous() and y_grouped.shape[1] == h.H
+        assert inv_perm.dtype == torch.int32 and inv_perm.is_contiguous() and tuple(inv_perm.shape) == (h.num_recv, h.K)
+        if topk_weights is not None:
+            assert topk_weights.dtype == torch.float32 and topk_weights.is_contiguous()
+            assert tuple(topk_weights.shape) == (h.num_recv, h.K)
+        if out is None:
+            out = torch.empty((h.T, h.H), dtype=torch.bfloat16, device=y_grouped.device)
+        assert out.dtype == torch.bfloat16 and out.is_contiguous() and tuple(out.shape) == (h.T, h.H)
+        L.check(
+            self.lib.b200ep_ht_combine_permuted(self.ctx, h.slot, _ptr(y_grouped), _ptr(inv_perm), _ptr(topk_weights),
+                                                _ptr(out), _ptr(h.layout.is_token_in_rank), _ptr(h.layout.send_off),
+                                                h.T, h.H, phases, _stream()),
+            "ht_combine_permuted",
+        )
+        return out
+
     # ------------------------------------------------------------ low latency
     @staticmethod
     def ll_size_hint(max_tokens_per_rank: int, hidden: int, world: int, num_experts: int) -> int:
@@ -542,6 +599,16 @@ class LocalWorld:
         for r in range(W):
             self.bufs[r].combine(ys[r], handles[r], res[r], L.PHASE_RECV)
         return res
+
+    def combine_permuted(self, ys_grouped, inv_perms, handles, topk_weights=None):
+        W = self.world
+        outs = [torch.empty((handles[r].T, handles[r].H), dtype=torch.bfloat16, device=ys_grouped[r].device)
+                for r in range(W)]
+        for ph in (L.PHASE_SEND, L.PHASE_RECV):
+            for r in range(W):
+                self.bufs[r].combine_permuted(ys_grouped[r], inv_perms[r], handles[r], outs[r],
+                                              topk_weights=None if topk_weights is None else topk_weights[r], phases=ph)
+        return outs
 
     def low_latency_dispatch(self, xs, topk_idx, max_tok, num_experts, *, use_fp8=True, ue8m0=False):
         W = self.world

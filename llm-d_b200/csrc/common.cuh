@@ -454,6 +454,16 @@ struct LocalScratch {
   HtMeta ht[kNumSlots];
   unsigned long long epoch[kNumFlagCat][kNumSlots];          // call epochs, advanced on the device
 };
+// private scratch of the expert-grouped permute's plan kernel (permute.cu): block ticket, finished blocks, call tag and the
+// per-(block, local expert) totals the blocks publish to each other, tagged by the call (never cleared)
+constexpr size_t kPermPubWords = (size_t)1 << 19;
+struct PermScratch {
+  unsigned long long ticket;
+  unsigned done, pad0;
+  unsigned long long epoch;
+  unsigned long long pad1[5];
+  unsigned long long pub[kPermPubWords];
+};
 // pinned host mirror of the count exchange result
 // Every word is (low 32 bits of the call epoch << 32 | value): one 8-byte store is atomic over PCIe, so
 // the host can tell a fresh word from a stale one without the device issuing a system fence first.
@@ -475,6 +485,7 @@ struct b200ep_ctx {
   bool ipc_open[b200ep::kMaxRanks];
   bool connected;
   b200ep::LocalScratch* local;   // device
+  b200ep::PermScratch* perm;     // device
   char* ll_local;                // device scratch for low-latency tables
   size_t ll_local_bytes;
   b200ep::HostMirror* host;      // pinned, mapped

@@ -34,6 +34,7 @@
 // Cross-GPU ordering: payload stores -> cp.async.bulk.wait_group -> atom.acq_rel.gpu
 // on a counter -> (last arrival) ONE fence.acq_rel.sys -> st.relaxed.sys flag in
 // every peer; consumers spin with ld.acquire.sys.
+#include "ht_types.cuh"
 #include "notify.cuh"
 
 namespace b200ep {
@@ -390,33 +391,7 @@ __global__ void __launch_bounds__(256) ht_dispatch_recv_kernel(const __grid_cons
     out_src[i] = __ldcg(reinterpret_cast<const int32_t*>(side0 + (size_t)i * side_bytes + side_src_off(K)));
 }
 
-// ------------------------------------------------------------------ combine
-struct HtCombineArgs {
-  Peers peers;
-  HtPlan plan;
-  const void* y;    // bf16 [M, H]
-  void* out;        // bf16 [T, H]
-  const uint8_t* in_rank;
-  const int32_t* send_off;
-  const HtMeta* meta;
-  unsigned* done;
-  size_t slot_off;
-  unsigned long long* epoch_ptr;
-  unsigned* chunk_done;  // [kCombChunks] private counters of the overlapped kernel
-  unsigned* red_next;    // [kCombChunks] next reduce item of each chunk, [kCombChunks] = warps finished
-  unsigned* piece_next;  // [kCombChunks] next DMA piece of each chunk (pieces are handed out from a queue)
-  int T, W, me, slot;
-  unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
-  int rows_per_piece;    // rows one DMA piece moves (<= stage size)
-  unsigned stage_bytes;  // bytes of one DMA stage
-};
-
-// Stage on the SOURCE rank: stage[dst rank d][p] = the row rank d returns for the p-th token this
-// rank sent to d (p = send_off[t][d]).  Rank d holds those rows contiguously, in the same order, as
-// rows [rank_prefix[s], rank_prefix[s+1]) of its receive order -- so the push is a block copy.
-__device__ __forceinline__ size_t stage_row_off(const HtPlan& p, int d, int pos, int row_bytes) {
-  return p.off_stage + ((size_t)d * p.t_cap + pos) * row_bytes;
-}
+// ------------------------------------------------------------------ combine (argument block: ht_types.cuh)
 
 // ---- software DMA: one thread moves pieces global -> shared -> peer global with TMA bulk copies.
 // kDmaStages stages; loads run kDmaAhead pieces ahead of stores; a stage is loaded again only after the
@@ -583,8 +558,8 @@ __device__ __forceinline__ unsigned reduce_resolve(const HtCombineArgs& a, const
   const char* rowp = nullptr;
   if (lane < W && a.in_rank[(size_t)t * W + lane]) {
     const int pos = a.send_off[(size_t)t * W + lane];
-    rowp = lane == a.me ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + pos) * row_bytes
-                        : stage + ((size_t)lane * a.plan.t_cap + pos) * row_bytes;
+    rowp = (lane == a.me && !a.self_staged) ? reinterpret_cast<const char*>(a.y) + (size_t)(my_first + pos) * row_bytes
+                                            : stage + ((size_t)lane * a.plan.t_cap + pos) * row_bytes;
   }
   const unsigned dmask = __ballot_sync(0xffffffffu, rowp != nullptr);
 #pragma unroll
@@ -1081,19 +1056,15 @@ extern "C" int b200ep_ht_views(b200ep_ctx* c, int slot, b200ep_ht_view* out) {
   return B200EP_OK;
 }
 
-extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, void* dev_out,
-                                 const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H,
-                                 int phases, void* stream) {
-  int rc = check_slot(c, slot, "ht_combine");
-  if (rc) return rc;
+namespace b200ep {
+int ht_combine_args(b200ep_ctx* c, int slot, const void* dev_y, void* dev_out, const uint8_t* dev_is_token_in_rank,
+                    const int32_t* dev_send_off, int T, int H, HtCombineArgs* out) {
   const HtPlan& plan = c->ht_plan[slot];
   if (plan.H == 0 || plan.H != H || T != c->ht_tokens[slot]) {
     set_error("ht_combine: no matching dispatch on slot %d (H=%d/%d, T=%d/%d)", slot, H, plan.H, T, c->ht_tokens[slot]);
     return B200EP_ERR_STATE;
   }
-  cudaStream_t st = (cudaStream_t)stream;
-  B200EP_CUDA(cudaSetDevice(c->device));
-  HtCombineArgs a;
+  HtCombineArgs& a = *out;
   a.peers = c->peers;
   a.plan = plan;
   a.y = dev_y;
@@ -1113,6 +1084,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   a.chunk_done = &c->local->done[16 + slot * kCombChunks];
   a.red_next = &c->local->done[32 + slot * 16];
   a.piece_next = &c->local->done[72 + slot * 16];
+  a.self_staged = 0;
   const int row_bytes = 2 * H;
   // DMA pieces: as many whole rows as fit 15 KB (one DeepSeek row; the probe gives 660-665 GB/s for 14 KB pieces and
   // 677 GB/s for 42 KB ones at EP=8, but small pieces keep the fabric queue shallow and the chunk flags timely)
@@ -1121,6 +1093,31 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
   static const int piece_env = getenv("B200EP_HT_PIECE_ROWS") ? atoi(getenv("B200EP_HT_PIECE_ROWS")) : 0;
   if (piece_env > 0 && (size_t)piece_env * row_bytes * kDmaStages <= 200 * 1024) a.rows_per_piece = piece_env;
   a.stage_bytes = (unsigned)a.rows_per_piece * (unsigned)row_bytes;
+  return B200EP_OK;
+}
+
+// RECV phase at W > 1: wait for every peer's push, then the fp32 reduction in rank order.
+int ht_combine_launch_recv(b200ep_ctx* c, const HtCombineArgs& a, cudaStream_t st) {
+  const int row_bytes = 2 * a.plan.H;
+  const int nsplit = row_bytes / 16 >= 256 ? 2 : 1;
+  if (c->world == 2) ht_combine_recv_kernel<2><<<grid_for(c, (long long)a.T * nsplit, 8, 3), 256, 0, st>>>(a);
+  else ht_combine_recv_kernel<kMaxRanks><<<grid_for(c, (long long)a.T * nsplit, 8, 2), 256, 0, st>>>(a);
+  B200EP_CUDA(cudaGetLastError());
+  return B200EP_OK;
+}
+}  // namespace b200ep
+
+extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, void* dev_out,
+                                 const uint8_t* dev_is_token_in_rank, const int32_t* dev_send_off, int T, int H,
+                                 int phases, void* stream) {
+  int rc = check_slot(c, slot, "ht_combine");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  B200EP_CUDA(cudaSetDevice(c->device));
+  HtCombineArgs a;
+  rc = ht_combine_args(c, slot, dev_y, dev_out, dev_is_token_in_rank, dev_send_off, T, H, &a);
+  if (rc) return rc;
+  const int row_bytes = 2 * H;
   const size_t dma_smem = (size_t)kDmaStages * a.stage_bytes;
   const bool any = phases & (B200EP_PHASE_SEND | B200EP_PHASE_RECV);
   if (any && T > 0 && (!dev_out || !dev_is_token_in_rank || !dev_send_off) && (phases & B200EP_PHASE_RECV)) {
@@ -1165,12 +1162,7 @@ extern "C" int b200ep_ht_combine(b200ep_ctx* c, int slot, const void* dev_y, voi
     ht_combine_send_kernel<<<grid, 128, dma_smem, st>>>(a);
     B200EP_CUDA(cudaGetLastError());
   }
-  if (phases & B200EP_PHASE_RECV) {
-    const int nsplit = row_bytes / 16 >= 256 ? 2 : 1;
-    if (c->world == 2) ht_combine_recv_kernel<2><<<grid_for(c, (long long)T * nsplit, 8, 3), 256, 0, st>>>(a);
-    else ht_combine_recv_kernel<kMaxRanks><<<grid_for(c, (long long)T * nsplit, 8, 2), 256, 0, st>>>(a);
-    B200EP_CUDA(cudaGetLastError());
-  }
+  if (phases & B200EP_PHASE_RECV) return ht_combine_launch_recv(c, a, st);
   return B200EP_OK;
 }
 

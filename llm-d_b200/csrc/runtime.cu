@@ -170,6 +170,7 @@ static void free_ctx(b200ep_ctx* c, cudaError_t* first_err) {
     if (c->ipc_open[r]) note(cudaIpcCloseMemHandle(c->peers.base[r]));
   if (c->sym) note(cudaFree(c->sym));
   if (c->local) note(cudaFree(c->local));
+  if (c->perm) note(cudaFree(c->perm));
   if (c->ll_local) note(cudaFree(c->ll_local));
   if (c->host) note(cudaFreeHost((void*)c->host));
   delete c;
@@ -215,6 +216,8 @@ int b200ep_create(b200ep_ctx** out, int rank, int world, int device, size_t sym_
   CREATE_CUDA(cudaMemset(c->sym, 0, kCtrlBytes));
   CREATE_CUDA(cudaMalloc(&c->local, sizeof(LocalScratch)));
   CREATE_CUDA(cudaMemset(c->local, 0, sizeof(LocalScratch)));
+  CREATE_CUDA(cudaMalloc(&c->perm, sizeof(PermScratch)));
+  CREATE_CUDA(cudaMemset(c->perm, 0, sizeof(PermScratch)));
   c->ll_local_bytes = 4 << 20;
   CREATE_CUDA(cudaMalloc(&c->ll_local, c->ll_local_bytes));
   CREATE_CUDA(cudaMemset(c->ll_local, 0, c->ll_local_bytes));
