@@ -64,6 +64,7 @@ class HtHandle:
     keep: Any = None  # tensors that must outlive the asynchronous kernels
     num_recv_dev: Any = None         # host-sync-free dispatch: rows received, device int32 scalar
     recv_per_expert_dev: Any = None  # host-sync-free dispatch: per-local-expert counts, device int32 [E/W]
+    deferred: Any = None             # (y_grouped, inv_perm, weights) left by a deferred unpermute: the combine gathers itself
 
 
 @dataclass
@@ -107,6 +108,11 @@ class _HtSlotState:
                 self.vcache.clear()
             v = self.vcache[M] = (fx[:M], (None if fs is None else fs[:M]), fi[:M], fw[:M], fr[:M])
         return v
+
+
+# recv_x.data_ptr() -> (Buffer, HtHandle) of the latest dispatch on that slot: lets code that only sees the received
+# tensor (vLLM's expert classes) find the dispatch it came from (b200ep.vllm_backend.deepgemm_moe_permute)
+_RECV_REGISTRY: dict = {}
 
 
 def exchange_handles(group, mine: bytes) -> bytes:
@@ -176,6 +182,8 @@ class Buffer:
     def destroy(self):
         if not self._destroyed:
             self._destroyed = True
+            for k in [k for k, v in _RECV_REGISTRY.items() if v[0] is self]:
+                del _RECV_REGISTRY[k]
             self._sym = None
             L.check(self.lib.b200ep_destroy(self.ctx), "destroy")
 
@@ -294,7 +302,9 @@ class Buffer:
             self.ht_notify(h.slot, h.layout)
             per_expert = self._dispatch_after_notify(h)
             self.ht_dispatch_launch(h, *args, L.PHASE_ALL)
-            return (*self.ht_views(h)[:4], per_expert, h)
+            views = self.ht_views(h)
+            _RECV_REGISTRY[views[0].data_ptr()] = (self, h)
+            return (*views[:4], per_expert, h)
         # no layout given: layout + count exchange + payload in ONE C call (b200ep_ht_dispatch_all)
         T, H = x.shape
         K = topk_idx.shape[1]
@@ -324,9 +334,13 @@ class Buffer:
                 raise L.B200EPError(f"num_worst_tokens={num_worst_tokens} exceeds the slot capacity of {st.full[2]} rows")
             h = HtHandle(slot, T, H, K, num_experts, kind, st.lay, int(num_worst_tokens), [], keep)
             h.num_recv_dev, h.recv_per_expert_dev = st.num_recv_dev, st.recv_per_expert_dev
-            return (*st.views(h.num_recv)[:4], [], h)
+            views = st.views(h.num_recv)
+            _RECV_REGISTRY[views[0].data_ptr()] = (self, h)
+            return (*views[:4], [], h)
         h = HtHandle(slot, T, H, K, num_experts, kind, st.lay, st.n.value, st.rp[:], keep)
-        return (*st.views(h.num_recv)[:4], st.pe[:], h)
+        views = st.views(h.num_recv)
+        _RECV_REGISTRY[views[0].data_ptr()] = (self, h)
+        return (*views[:4], st.pe[:], h)
 
     def _ht_slot_state(self, slot, T, H, K, E, kind, dev):
         """Everything a dispatch on `slot` needs that does not change from call to call while the shape stays
@@ -446,6 +460,7 @@ class Buffer:
                                        _ptr(expert_ids), _ptr(inv_perm), None, m_cap, _stream()),
             "ht_permute",
         )
+        h._inv_ptr = inv_perm.data_ptr()  # lets a deferred unpermute recognise its own inv_perm (vllm_backend)
         return out_x[:m_cap], (None if bf16 else out_scales[:m_cap]), expert_ids, inv_perm
 
     def combine_permuted(self, y_grouped: torch.Tensor, inv_perm: torch.Tensor, handle: HtHandle, out=None, *,

@@ -133,8 +133,61 @@ def get_classes():
     return _classes
 
 
+# ---------------------------------------------------------------------------------------------
+# Expert-grouped layout without the Triton passes.  Drop-in replacements, same
+# signatures, for the two functions DeepGemmExperts.apply calls around its grouped GEMMs
+# (vllm/model_executor/layers/fused_moe/experts/deep_gemm_moe.py:279-291, 322-329; defined in
+# fused_moe/deep_gemm_utils.py:347-440).  Rows that did not come from a b200ep dispatch fall through to
+# vLLM's own functions.
+
+
+def deepgemm_moe_permute(aq, aq_scale, topk_ids, local_num_experts, expert_map, expert_tokens_meta, aq_out=None):
+    """``deepgemm_moe_permute`` on the rows a b200ep dispatch received: one plan kernel + one scatter kernel
+    (b200ep_ht_permute) instead of ep_scatter's two Triton kernels, the fill of expert_ids and the count pass;
+    rows inside an expert come out in received order (deterministic)."""
+    from vllm.model_executor.layers.fused_moe import deep_gemm_utils as dgu
+
+    from .buffer import _RECV_REGISTRY
+
+    ent = _RECV_REGISTRY.get(aq.data_ptr())
+    if ent is None or tuple(aq.shape) != (ent[1].num_recv, ent[1].H) or aq.dtype != torch.float8_e4m3fn:
+        return dgu.deepgemm_moe_permute(aq, aq_scale, topk_ids, local_num_experts, expert_map, expert_tokens_meta, aq_out)
+    buf, h = ent
+    block_m = dgu.get_mk_alignment_for_contiguous_layout()[0]
+    per_expert = None
+    if expert_tokens_meta is not None and expert_tokens_meta.expert_num_tokens_cpu is not None:
+        per_expert = expert_tokens_meta.expert_num_tokens_cpu.tolist()
+    a_perm, s_perm, expert_ids, inv_perm = buf.ht_permute(h, alignment=block_m, per_expert=per_expert, out_x=aq_out)
+    return a_perm, s_perm, expert_ids, inv_perm
+
+
+def deepgemm_unpermute_and_reduce(a, topk_ids, topk_weights, inv_perm, expert_map, output):
+    """``deepgemm_unpermute_and_reduce``, deferred: when ``inv_perm`` came from the function above, nothing runs here.
+    The grouped GEMM output stays where it is and the combine that follows (deep_ep.Buffer.combine on the handle of
+    the same dispatch) gathers, weights and reduces inside its push (b200ep_ht_combine_permuted); ``output`` is not
+    written, and the combine ignores it."""
+    from vllm.model_executor.layers.fused_moe import deep_gemm_utils as dgu
+
+    from .buffer import _RECV_REGISTRY
+
+    for buf, h in list(_RECV_REGISTRY.values()):
+        if tuple(inv_perm.shape) == (h.num_recv, h.K) and inv_perm.dtype == torch.int32 and getattr(h, "_inv_ptr", 0) == inv_perm.data_ptr():
+            w = topk_weights.to(torch.float32).contiguous()
+            h.deferred = (a, inv_perm, w)
+            return None
+    return dgu.deepgemm_unpermute_and_reduce(a, topk_ids, topk_weights, inv_perm, expert_map, output)
+
+
 def install() -> None:
-    """vLLM general-plugin hook: make maybe_make_prepare_finalize build the fused class."""
+    """vLLM general-plugin hook: make maybe_make_prepare_finalize build the fused class, and let the DeepGEMM experts
+    regroup received rows / return results through b200ep instead of ep_scatter / ep_gather."""
     import vllm.model_executor.layers.fused_moe.all2all_utils as a2a
 
     a2a.DeepEPHTPrepareAndFinalize = get_classes()["B200EPHTPrepareAndFinalize"]
+    try:
+        import vllm.model_executor.layers.fused_moe.experts.deep_gemm_moe as dgm
+
+        dgm.deepgemm_moe_permute = deepgemm_moe_permute
+        dgm.deepgemm_unpermute_and_reduce = deepgemm_unpermute_and_reduce
+    except Exception:  # the experts module needs more than this backend does; the P&F swap above still stands
+        pass

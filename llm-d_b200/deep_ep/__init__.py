@@ -187,8 +187,15 @@ class Buffer:
         if topk_weights is not None or bias is not None:
             raise NotImplementedError("b200ep: combine(topk_weights=..., bias=...) is not used by vLLM (deepep_ht.py:367-376)")
         compute = self._enter_comm(previous_event)
+        deferred, handle.deferred = getattr(handle, "deferred", None), None
         with torch.cuda.stream(self._comm):
-            out = self._impl.combine(x.contiguous(), handle)
+            if deferred is not None:
+                # the experts left their grouped GEMM output in place (b200ep.vllm_backend.deepgemm_unpermute_and_reduce):
+                # gather + weighted reduction happen inside the push, `x` was never written
+                y_grouped, inv_perm, weights = deferred
+                out = self._impl.combine_permuted(y_grouped, inv_perm, handle, topk_weights=weights)
+            else:
+                out = self._impl.combine(x.contiguous(), handle)
         ev = self._leave_comm(compute, async_finish, (x, out))
         return out, None, ev
 

@@ -168,3 +168,71 @@ def test_permute_full_size_world8_shape():
         assert err <= 0.08 * ref.abs().max().item(), err
     finally:
         world.destroy()
+
+
+def test_route_b_drop_ins_against_vllm_functions(monkeypatch):
+    """Route B: b200ep.vllm_backend.deepgemm_moe_permute / deepgemm_unpermute_and_reduce called exactly as
+    DeepGemmExperts.apply calls vLLM's functions of the same names (deep_gemm_moe.py:279-291,322-329), on rows
+    received through the deep_ep shim; the deferred unpermute is picked up by deep_ep.Buffer.combine.  Reference:
+    vLLM's own two functions + the plain combine on the same dispatch."""
+    dgu = pytest.importorskip("vllm.model_executor.layers.fused_moe.deep_gemm_utils")
+    import torch.distributed as dist
+    import vllm.model_executor.layers.fused_moe.modular_kernel as mk
+
+    import deep_ep
+    from b200ep import vllm_backend as vb
+
+    monkeypatch.setattr(dgu, "get_mk_alignment_for_contiguous_layout", lambda: [128, 128])  # DeepGEMM is not installed here
+    if not dist.is_initialized():
+        dist.init_process_group("gloo", rank=0, world_size=1, init_method="tcp://127.0.0.1:29547")
+    torch.cuda.set_device(0)
+    T, H, E, K = 700, 2048, 64, 8
+    x, ids, w = make_rank_inputs(T, H, E, K, seed=21, mask_frac=0.1)
+    buf = deep_ep.Buffer(group=dist.group.WORLD, num_nvl_bytes=1 << 30, num_rdma_bytes=0, low_latency_mode=False,
+                         num_qps_per_rank=1, explicitly_destroy=True)
+    try:
+        tpr, _, tpe, inr, _ = buf.get_dispatch_layout(topk_idx=ids.to(DEV), num_experts=E)
+        (rx, rs), ridx, rw, per_expert, handle, _ = buf.dispatch(
+            x=x.to(DEV), num_tokens_per_rank=tpr, is_token_in_rank=inr, num_tokens_per_expert=tpe, topk_idx=ids.to(DEV),
+            topk_weights=w.to(DEV), b200ep_quantize=True)
+        meta = mk.ExpertTokensMetadata.make_from_list(per_expert, device=DEV)
+        m_sum = dgu.compute_aligned_M(rx.shape[0], K, E, 128, meta)
+        ws = torch.empty((m_sum, H), dtype=torch.float8_e4m3fn, device=DEV)
+        a1, s1, e1, inv1 = vb.deepgemm_moe_permute(aq=rx, aq_scale=rs, topk_ids=ridx, local_num_experts=E, expert_map=None,
+                                                   expert_tokens_meta=meta, aq_out=ws)
+        assert a1.data_ptr() == ws.data_ptr() and a1.shape == (m_sum, H)
+        a0, s0, e0, inv0 = dgu.deepgemm_moe_permute(aq=rx, aq_scale=rs, topk_ids=ridx, local_num_experts=E, expert_map=None,
+                                                    expert_tokens_meta=meta)
+        torch.cuda.synchronize()
+        assert torch.equal(e0, e1)
+        ok = ridx >= 0
+        m_of = torch.arange(rx.shape[0], device=DEV)[:, None].expand(-1, K)[ok]
+        for a, s, inv in ((a1, s1, inv1), (a0, s0, inv0)):  # both layouts hold every entry's row at inv_perm
+            assert torch.equal(a.view(torch.uint8)[inv[ok].long()], rx.view(torch.uint8)[m_of])
+            assert torch.equal(s[inv[ok].long()], rs[m_of])
+        g = torch.Generator().manual_seed(9)
+        y_entry = torch.randn(rx.shape[0], K, H, generator=g).to(torch.bfloat16).to(DEV)
+        mm_ours = torch.zeros((m_sum, H), dtype=torch.bfloat16, device=DEV)
+        mm_ref = torch.zeros((m_sum, H), dtype=torch.bfloat16, device=DEV)
+        mm_ours[inv1[ok].long()] = y_entry[ok]
+        mm_ref[inv0[ok].long()] = y_entry[ok]
+        out_ref = torch.empty((rx.shape[0], H), dtype=torch.bfloat16, device=DEV)
+        dgu.deepgemm_unpermute_and_reduce(a=mm_ref, topk_ids=ridx, topk_weights=rw, inv_perm=inv0, expert_map=None,
+                                          output=out_ref)
+        comb_ref, _, _ = buf.combine(x=out_ref, handle=handle)
+        comb_ref = comb_ref.clone()
+        out_unused = torch.full((rx.shape[0], H), float("nan"), dtype=torch.bfloat16, device=DEV)
+        assert vb.deepgemm_unpermute_and_reduce(a=mm_ours, topk_ids=ridx, topk_weights=rw, inv_perm=inv1, expert_map=None,
+                                                output=out_unused) is None
+        assert handle.deferred is not None
+        comb, _, _ = buf.combine(x=out_unused, handle=handle)
+        torch.cuda.synchronize()
+        assert handle.deferred is None
+        assert torch.equal(comb.view(torch.int16), comb_ref.view(torch.int16))
+        # rows that did not come from a b200ep dispatch fall through to vLLM's function
+        other = rx.clone()
+        a2, _, e2, _ = vb.deepgemm_moe_permute(aq=other, aq_scale=rs, topk_ids=ridx, local_num_experts=E, expert_map=None,
+                                               expert_tokens_meta=meta)
+        assert torch.equal(e2, e0)
+    finally:
+        buf.destroy()
