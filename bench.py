@@ -473,7 +473,7 @@ def main():
         buf.combine(y, h, out)
         if args.breakdown and timed:
             m[2].record(); marks.append((m, th1 - th0, time.perf_counter() - th1))
-        last["h"], last["a"], last["y"] = h, (xs[b], None, idss[b], wss[b], False), y
+        last["h"], last["a"], last["y"], last["pe"] = h, (xs[b], None, idss[b], wss[b], False), y, per_expert
         if timed:
             remote_copies.append(h.num_recv - (h.rank_prefix[rank + 1] - h.rank_prefix[rank]))
 
@@ -553,6 +553,43 @@ def main():
         buf.combine(y, h, out, L.PHASE_RECV); e2.record()
         k_comb.append((e0, e2)); k_csend.append((e0, e1))
     torch.cuda.synchronize()
+    barrier()
+    # ---- expert-grouped layout: regroup the received rows by local expert (replaces vLLM's ep_scatter)
+    # and combine straight from the grouped GEMM output with the weighted fp32 reduction inside the push (replaces
+    # ep_gather + Buffer.combine).  Informative: event-timed like the kernels above, max over ranks.
+    grouped = None
+    try:
+        a_perm, s_perm, eids, inv = buf.ht_permute(h, per_expert=last["pe"])
+        y_grp = torch.randn(a_perm.shape[0], H, device=dev).to(torch.bfloat16)
+        g_perm, g_comb = [], []
+        for _ in range(R):
+            flush.amax()
+            e0, e1 = ev(), ev()
+            e0.record(); buf.ht_permute(h, per_expert=last["pe"], out_x=a_perm, out_scales=s_perm); e1.record()
+            g_perm.append((e0, e1))
+        for _ in range(R):
+            flush.amax()
+            e0, e1 = ev(), ev()
+            e0.record(); buf.combine_permuted(y_grp, inv, h, out, phases=L.PHASE_SEND)
+            buf.combine_permuted(y_grp, inv, h, out, phases=L.PHASE_RECV); e1.record()
+            g_comb.append((e0, e1))
+        torch.cuda.synchronize()
+        gt = torch.tensor([sum(p.elapsed_time(q) for p, q in g_perm) / R, sum(p.elapsed_time(q) for p, q in g_comb) / R],
+                          device=dev)
+        if world > 1:
+            dist.all_reduce(gt, op=dist.ReduceOp.MAX)
+        entries = int(sum(last["pe"]))
+        perm_bytes = (h.num_recv + entries) * (H + 4 * H // 128)
+        grouped = {
+            "permute_ms": float(gt[0].item()), "rows_in": h.num_recv, "rows_out": entries, "m_sum": int(a_perm.shape[0]),
+            "permute_algorithmic_bytes": perm_bytes, "permute_hbm_gbs": perm_bytes / (float(gt[0].item()) * 1e-3) / 1e9,
+            "combine_permuted_ms": float(gt[1].item()),
+            "what": "rank 0's row counts; permute = plan + scatter kernels (rows read once, written once per local expert); "
+                    "combine_permuted = gather + fp32 weighted reduce + push, then the fp32 reduce on the source (two launches)",
+        }
+        del y_grp, a_perm, s_perm
+    except Exception as ex:  # informative block: never lose the headline over it
+        grouped = {"error": repr(ex)[:300]}
     barrier()
     del flush
     if args.breakdown:
@@ -709,7 +746,7 @@ def main():
             # kernels of libb200ep.so inside the timed region: per step layout + dispatch + combine (EP=1), plus the
             # receive-side unpack kernel at EP>1
             "gpu_launches": steps * (3 if world == 1 else 4), "ll": ll,
-            "host_sync_free": nosync, "parity": parity_res,
+            "host_sync_free": nosync, "grouped": grouped, "parity": parity_res,
         }
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     buf.destroy()

@@ -248,6 +248,7 @@ struct GatherArgs {
   const long long* recv_idx;  // [M, K] local ids or -1
   const float* recv_w;        // [M, K]
   int K;
+  int nparts;                 // W > 1: a row is pushed in this many parts (one warp each)
 };
 
 constexpr int kGatU = 4;  // 16-byte vectors per lane and batch
@@ -305,23 +306,29 @@ __device__ __forceinline__ void gather_batch(const char* y, int row_bytes, unsig
   }
 }
 
-// W > 1, phase SEND.  A warp per received row, two shared-memory stages per warp: gather + reduce into the stage,
-// one TMA bulk copy to stage[me][position] on the source rank (this rank's own rows go to its own stage the same
-// way: the reduction then reads every rank's row from the stage).  Items interleave the destinations, starting
-// with rank me+1, so that the ranks push along a permutation at any moment.
+// W > 1, phase SEND.  A warp per (received row, part of the row), two shared-memory stages per warp: gather +
+// reduce into the stage, one TMA bulk copy to stage[me][position] on the source rank (this rank's own rows go to
+// its own stage the same way: the reduction then reads every rank's row from the stage).  Rows are cut into
+// `nparts` parts of at most 8 KB so that twice as many warps fit the shared memory: a warp's work is a chain of
+// dependent memory round trips (one per batch and pair of experts), so the push is fed by warps in flight, not by
+// bytes per warp.  Items interleave the destinations, starting with rank me+1, so that the ranks push along a
+// permutation at any moment.
 __global__ void __launch_bounds__(512, 1) ht_combine_gather_send_kernel(const __grid_constant__ GatherArgs g) {
   extern __shared__ __align__(128) char s_mem[];
   const HtCombineArgs& a = g.c;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int W = a.W, K = g.K, row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
-  char* s_stage = s_mem + (size_t)warp * 2 * row_bytes;
+  const int nparts = g.nparts, part_vec = (nvec + nparts - 1) / nparts, part_bytes = part_vec * 16;
+  char* s_stage = s_mem + (size_t)warp * 2 * part_bytes;
   int maxcnt = 0;
   for (int s = 0; s < W; ++s) maxcnt = max(maxcnt, a.meta->rank_prefix[s + 1] - a.meta->rank_prefix[s]);
-  const long long total = (long long)maxcnt * W;
+  const long long total = (long long)maxcnt * W * nparts;
   const char* y = reinterpret_cast<const char*>(a.y);
-  int n = 0;  // rows this warp has staged
+  int n = 0;  // parts this warp has staged
   for (long long it = (long long)blockIdx.x * nwarp + warp; it < total; it += (long long)gridDim.x * nwarp) {
-    const int s = (a.me + 1 + (int)(it % W)) % W, j = (int)(it / W);
+    const int part = (int)(it % nparts);
+    const long long rit = it / nparts;
+    const int s = (a.me + 1 + (int)(rit % W)) % W, j = (int)(rit / W);
     const int first = a.meta->rank_prefix[s];
     if (j >= a.meta->rank_prefix[s + 1] - first) continue;  // uniform over the warp
     const int m = first + j;
@@ -335,23 +342,25 @@ __global__ void __launch_bounds__(512, 1) ht_combine_gather_send_kernel(const __
       }
     }
     const unsigned kmask = __ballot_sync(0xffffffffu, my_dst >= 0);
-    char* st = s_stage + (size_t)(n & 1) * row_bytes;
+    char* st = s_stage + (size_t)(n & 1) * part_bytes;
     ++n;
     if (lane == 0) bulk_wait_read1();  // the copy that last used this stage has finished reading it
     __syncwarp();
-    for (int v0 = 0; v0 < nvec; v0 += 32 * kGatU) {
+    const int vbeg = part * part_vec, vend = min(nvec, vbeg + part_vec);
+    for (int v0 = vbeg; v0 < vend; v0 += 32 * kGatU) {
       float acc[kGatU][8];
-      gather_batch(y, row_bytes, kmask, my_dst, my_w, v0, nvec, lane, acc);
+      gather_batch(y, row_bytes, kmask, my_dst, my_w, v0, vend, lane, acc);
 #pragma unroll
       for (int jj = 0; jj < kGatU; ++jj) {
         const int v = v0 + jj * 32 + lane;
-        if (v < nvec) reinterpret_cast<int4*>(st)[v] = pack8_bf16_rn(acc[jj]);
+        if (v < vend) reinterpret_cast<int4*>(st)[v - vbeg] = pack8_bf16_rn(acc[jj]);
       }
     }
     fence_proxy_async_smem();
     __syncwarp();
     if (lane == 0) {
-      bulk_s2g(a.peers.base[s] + a.slot_off + stage_row_off(a.plan, a.me, j, row_bytes), st, row_bytes);
+      bulk_s2g(a.peers.base[s] + a.slot_off + stage_row_off(a.plan, a.me, j, row_bytes) + (size_t)vbeg * 16, st,
+               (uint32_t)(vend - vbeg) * 16);
       bulk_commit();
     }
   }
@@ -495,6 +504,7 @@ extern "C" int b200ep_ht_combine_permuted(b200ep_ctx* c, int slot, const void* d
   g.recv_idx = reinterpret_cast<const long long*>(base + plan.off_idx);
   g.recv_w = dev_topk_weights ? dev_topk_weights : reinterpret_cast<const float*>(base + plan.off_w);
   g.K = plan.K;
+  g.nparts = 1;
   g.c.self_staged = 1;
   if (T > 0 && (phases & B200EP_PHASE_RECV) && (!dev_out || !dev_send_off || (c->world > 1 && !dev_is_token_in_rank))) {
     set_error("ht_combine_permuted: null pointer");
@@ -519,13 +529,12 @@ extern "C" int b200ep_ht_combine_permuted(b200ep_ctx* c, int slot, const void* d
     return B200EP_OK;
   }
   if (phases & B200EP_PHASE_SEND) {
-    int warps = 200 * 1024 / (2 * row_bytes);
+    const int nvec = row_bytes / 16;
+    g.nparts = (row_bytes + 8191) / 8192;  // parts of at most 8 KB
+    const int part_bytes = (nvec + g.nparts - 1) / g.nparts * 16;
+    int warps = 200 * 1024 / (2 * part_bytes);
     if (warps > 16) warps = 16;
-    if (warps < 1) {
-      set_error("ht_combine_permuted: a row of %d bytes does not fit the shared-memory stages", row_bytes);
-      return B200EP_ERR_ARG;
-    }
-    const size_t smem = (size_t)warps * 2 * row_bytes;
+    const size_t smem = (size_t)warps * 2 * part_bytes;
     const int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
     B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_gather_send_kernel, c->device, (int)smem));
     ht_combine_gather_send_kernel<<<grid, warps * 32, smem, st>>>(g);

@@ -94,6 +94,9 @@ def run_gpu():
         parity.check_ht(buf, cpu_group, W, rank, dev, Ts, H, E, K, seed=7 + it, dist=kind,
                         id_dtype=(torch.int32 if it % 4 == 1 else torch.int64), mask_frac=(0.2 if it % 5 == 2 else 0.0),
                         ue8m0=(it % 7 == 3), nosync=(it % 4 == 2))
+        if it % 3 == 0:  # expert-grouped layout + combine from it, interleaved with the plain calls (shared slots, epochs)
+            parity.check_ht_grouped(buf, cpu_group, W, rank, dev, Ts, H, E, K, seed=40 + it, dist=kind,
+                                    mask_frac=(0.2 if it % 2 else 0.0))
     for E_ll in (64, 288):
         if E_ll % W:
             continue
@@ -170,6 +173,7 @@ def run_gpu_full():
     for it, kind in enumerate(("uniform", "zipf", "one_rank")):
         parity.check_ht(buf, cpu_group, W, rank, dev, [T] * W, H, E, K, seed=50 + it, dist=kind, combine_out=out)
         parity.check_ht(buf, cpu_group, W, rank, dev, [T] * W, H, E, K, seed=60 + it, dist=kind, nosync=True, combine_out=out)
+    parity.check_ht_grouped(buf, cpu_group, W, rank, dev, [T] * W, H, E, K, seed=70)
     for E_ll in (256, 288):
         if E_ll % W:
             continue

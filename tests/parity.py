@@ -23,7 +23,7 @@ import numpy as np
 import torch
 
 from _util import bf16_bits, bits_to_bf16, make_rank_inputs, u8
-from oracle import bits, combine, dispatch, fp8, layout
+from oracle import bits, combine, dispatch, fp8, layout, permute
 
 
 class ParityError(AssertionError):
@@ -118,6 +118,58 @@ def check_ht(buf, group, W, me, dev, Ts, H, E, K, seed, dist="uniform", *, nosyn
         parts.append((tok, bits.f32_to_bf16(deq[tok] * _ht_scale(d))))
     want = combine.ht_combine_source(Ts[me], H, parts)
     _eq(bf16_bits(out), want, f"{tag} combine output", me)
+    _agree(group, W, me)
+
+
+def check_ht_grouped(buf, group, W, me, dev, Ts, H, E, K, seed, dist="uniform", mask_frac=0.0):
+    """Dispatch, regroup the received rows by local expert (b200ep_ht_permute) and combine straight from the grouped
+    layout (b200ep_ht_combine_permuted, all phases): the calls a DeepGEMM expert class makes through Route B.
+    Expert stand-in: the grouped row of entry (t, k) on rank d, local expert e, answers bf16(dequant(row) * (1 + 0.125 d + 0.5 e))."""
+    el = E // W
+    x, ids, w = make_rank_inputs(Ts[me], H, E, K, seed * 100 + me, dist=dist, world=W, mask_frac=mask_frac)
+    q, s = fp8.group_quant_fp8(bf16_bits(x), fast=True)
+    allr = _gather(group, (q, s, ids.numpy(), w.numpy()), W)
+    ref = dispatch.ht_dispatch([a[0] for a in allr], [a[2] for a in allr], [a[3] for a in allr], E,
+                               scales=[a[1] for a in allr], dests=[me])[me]
+    p = permute.moe_permute(ref["recv_x"], ref["recv_x_scales"], ref["recv_topk_idx"], el, alignment=128)
+    rx, rs, ridx, rw, per_expert, h = buf.dispatch(x.to(dev), ids.to(dev), w.to(dev), E, quantize=True)
+    a_perm, s_perm, eids, inv = buf.ht_permute(h, per_expert=per_expert)
+    torch.cuda.synchronize()
+    tag = f"ht_grouped[{dist}, T={Ts[me]}]"
+    ok_shape = _eq([int(a_perm.shape[0]), int(inv.shape[0])], [p["m_sum"], ref["num_recv_tokens"]], f"{tag} sizes", me)
+    if ok_shape:
+        v = p["valid"]
+        _eq(u8(a_perm)[v], p["out_x"][v], f"{tag} grouped fp8 bytes", me)
+        _eq(s_perm.cpu().numpy().view(np.uint32)[v], p["out_scales"].view(np.uint32)[v], f"{tag} grouped scales", me)
+        _eq(eids.cpu().numpy(), p["expert_ids"], f"{tag} expert_ids", me)
+        _eq(inv.cpu().numpy(), p["inv_perm"], f"{tag} inv_perm", me)
+    # expert outputs in the grouped layout, from the ORACLE's layout (padding rows are poison: never read)
+    yg = np.full((int(a_perm.shape[0]), H), 0x7FC0, np.uint16)
+    if ok_shape and p["m_sum"]:
+        v = p["valid"]
+        f = (1.0 + 0.125 * me + 0.5 * p["expert_ids"][v]).astype(np.float32)
+        yg[v] = bits.f32_to_bf16(fp8.dequant_fp8(p["out_x"][v], p["out_scales"][v]) * f[:, None])
+    out = torch.full((Ts[me], H), float("nan"), dtype=torch.bfloat16, device=dev)
+    inv_dev = inv if ok_shape else torch.full((h.num_recv, K), -1, dtype=torch.int32, device=dev)
+    buf.combine_permuted(bits_to_bf16(yg, dev), inv_dev, h, out)
+    torch.cuda.synchronize()
+    # what MY tokens get back: per destination rank d, z = bf16(sum_k fma(row(t,k), w[t,k])) over d's experts, k ascending
+    idn, wn = ids.numpy().astype(np.int64), w.numpy()
+    deq = fp8.dequant_fp8(q, s)
+    in_rank = layout.dispatch_layout(ids.numpy(), E, W)[2]
+    parts = []
+    for d in range(W):
+        tok = np.nonzero(in_rank[:, d])[0]
+        acc = np.zeros((tok.size, H), np.float32)
+        for k in range(K):
+            e = idn[tok, k]
+            m = (e >= 0) & (e < E) & (e // el == d)
+            if m.any():
+                f = (1.0 + 0.125 * d + 0.5 * (e[m] % el)).astype(np.float32)
+                rows = bits.bf16_to_f32(bits.f32_to_bf16(deq[tok[m]] * f[:, None]))
+                acc[m] = permute.fma32(rows, wn[tok[m], k][:, None], acc[m])
+        parts.append((tok, bits.f32_to_bf16(acc)))
+    _eq(bf16_bits(out), combine.ht_combine_source(Ts[me], H, parts), f"{tag} combine output", me)
     _agree(group, W, me)
 
 
@@ -237,6 +289,9 @@ def run_bench_parity(buf, group, W, me, dev, barrier, *, H=7168, E=256, K=8, T_h
     for i, dist_kind in enumerate(("uniform", "one_rank")):
         check_ht(buf, group, W, me, dev, Ts, H, E, K, seed=720 + i, dist=dist_kind, nosync=True)
     res["ht_nosync"] = "ok"
+    for i, dist_kind in enumerate(("uniform", "zipf")):
+        check_ht_grouped(buf, group, W, me, dev, Ts, H, E, K, seed=730 + i, dist=dist_kind, mask_frac=0.1 * i)
+    res["ht_grouped"] = "ok"
     for ne in ll_experts:
         if ne % W:
             continue
