@@ -289,6 +289,124 @@ def run_nccl_agrs(args):
     return 0
 
 
+def run_flashinfer_a2a(args):
+    """On-box GPU comparator: FlashInfer's one-sided NVLink MoE all-to-all (flashinfer.comm.MoeAlltoAll,
+    the kernels behind vLLM's ``--all2all-backend flashinfer_nvlink_one_sided``), LIBRARY code, called the way vLLM calls
+    it (prepare_finalize/flashinfer_nvlink_one_sided.py:119-168): dispatch of fp8 rows + fp32 scales + int32 ids + fp32
+    weights, combine of bf16 rows; the workspace is FlashInfer's own (cuMem + POSIX fd exchange over the gloo group).
+    Same shapes as the b200ep arm: T=4096 per rank (throughput) and T=32..256 (decode, CUDA-graph replay when the ops
+    capture, else back-to-back launches).  Its JIT module is prebuilt for sm_100a under baseline/_fi_cache (no network)."""
+    os.environ.setdefault("FLASHINFER_WORKSPACE_BASE", os.path.join(ROOT, "baseline", "_fi_cache"))
+    os.environ.setdefault("FLASHINFER_CUDA_ARCH_LIST", "10.0a")
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        if rank == 0:
+            os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
+    if world < 2:
+        emit({"impl": "flashinfer_a2a", "unavailable": "needs at least 2 GPUs (torchrun --nproc-per-node N)"})
+        return 0
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    cpu_group = dist.new_group(backend="gloo")
+    try:
+        from flashinfer.comm import MoeAlltoAll
+        from flashinfer.comm.mapping import Mapping
+        from flashinfer.comm.mnnvl import MnnvlConfig, TorchDistBackend
+        from flashinfer.comm.trtllm_moe_alltoall import moe_a2a_get_workspace_size_per_rank
+
+        max_tok = T
+        disp_bytes = H + 4 * (H // 128) + K * 4 + K * 4
+        ws = moe_a2a_get_workspace_size_per_rank(ep_size=world, max_num_tokens=max_tok,
+                                                 total_dispatch_payload_size_per_token=disp_bytes,
+                                                 combine_payload_size_per_token=2 * H)
+        mapping = Mapping(world, rank, torch.cuda.device_count(), tp_size=world, moe_ep_size=world)
+        a2a = MoeAlltoAll(mapping=mapping, max_num_tokens=max_tok, top_k=K, num_experts=E, workspace_size_per_rank=ws,
+                          mnnvl_config=MnnvlConfig(comm_backend=TorchDistBackend(cpu_group)))
+    except Exception as ex:
+        emit({"impl": "flashinfer_a2a", "unavailable": f"FlashInfer MoeAlltoAll could not be set up on this box: {ex!r}"[:400]})
+        dist.destroy_process_group()
+        return 0
+    dist.barrier()
+
+    def make(tokens):
+        g = torch.Generator(device="cpu").manual_seed(1000 + rank)
+        xq = torch.randint(0, 255, (tokens, H), dtype=torch.uint8, generator=g).to(dev).view(torch.float8_e4m3fn)
+        xs = torch.rand(tokens, H // 128, generator=g).to(dev)
+        _, ids = torch.topk(torch.randn(tokens, E, generator=g), K, dim=-1)
+        w = torch.rand(tokens, K, generator=g).to(dev)
+        return xq, xs, ids.to(torch.int32).to(dev), w
+
+    def one(tokens, inp, y):
+        xq, xs, ids, w = inp
+        a2a.dispatch(token_selected_experts=ids, input_payloads=[xq, xs, ids, w], runtime_max_tokens_per_rank=tokens,
+                     invalid_token_expert_id=-1, expert_id_payload_index=2)
+        return a2a.combine(payload=y, runtime_max_tokens_per_rank=tokens)
+
+    def timed(tokens, iters, warm, graph):
+        inp = make(tokens)
+        y = torch.randn(world, tokens, H, device=dev).to(torch.bfloat16)
+        for _ in range(warm):
+            one(tokens, inp, y)
+        torch.cuda.synchronize(); dist.barrier()
+        g, how = None, "launches queued back to back"
+        if graph:
+            try:
+                st = torch.cuda.Stream(device=dev)
+                with torch.cuda.stream(st):
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=st, capture_error_mode="relaxed"):
+                        one(tokens, inp, y)
+                how = "CUDA graph of dispatch + combine, replayed"
+            except Exception:
+                g = None
+                a2a._state.phase = "idle"
+            torch.cuda.synchronize()
+        flag = torch.tensor([1 if g is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if not int(flag.item()):
+            g, how = None, "launches queued back to back"
+        dist.barrier()
+        samples = []
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+        for a, b in evs:
+            a.record()
+            g.replay() if g is not None else one(tokens, inp, y)
+            b.record()
+        torch.cuda.synchronize()
+        samples = sorted(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([samples[len(samples) // 2], sum(samples) / len(samples)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0].item()), float(t[1].item()), how
+
+    steps, warm = max(1, args.steps), max(3, args.warmup)
+    try:
+        _, ht_mean, _ = timed(T, steps, warm, graph=False)
+        ll = {}
+        for tok in (32, 64, 128, 256):
+            p50, _, how = timed(tok, 200, 10, graph=True)
+            ll[str(tok)] = {"p50_us": p50 * 1e3, "how": how}
+    except Exception as ex:
+        emit({"impl": "flashinfer_a2a", "unavailable": f"FlashInfer MoeAlltoAll failed while running: {ex!r}"[:400]})
+        os._exit(0)
+    emit({"impl": "flashinfer_a2a", "metric": METRIC, "value": world * T / (ht_mean * 1e-3), "unit": "tokens/s", "n_gpus": world,
+          "steps": steps, "warmup": warm, "ms_per_step": ht_mean, "higher_is_better": True, "scaling": "weak", "data": "synthetic",
+          "config": {"workload": WORKLOAD, "ep_size": world, "tokens_per_s_per_gpu": T / (ht_mean * 1e-3),
+                     "what": "flashinfer.comm.MoeAlltoAll dispatch (fp8 rows + fp32 scales + int32 ids + fp32 weights, already "
+                             "quantised: no quantise pass, no layout kernel) + combine (bf16), called as vLLM's "
+                             "flashinfer_nvlink_one_sided prepare/finalize does; library kernels, comparator only"},
+          "ll": ll, "deep_ep": "unavailable on this box (import deep_ep finds only the b200ep shim; DeepEP needs NVSHMEM)"})
+    torch.cuda.synchronize()
+    os._exit(0)  # FlashInfer's workspace teardown can hang at interpreter exit; the numbers are out
+
+
 def run_probe(args):
     """What NVLink gives SM-driven copies on this box: every rank
     moves 32 MiB to / from each peer between the symmetric regions, in pieces of the sizes the kernels use
@@ -394,6 +512,8 @@ def main():
         return run_nccl_agrs(args)
     if args.impl == "probe":
         return run_probe(args)
+    if args.impl == "flashinfer_a2a":
+        return run_flashinfer_a2a(args)
 
     import torch.distributed as dist
 

@@ -81,6 +81,7 @@ struct HtDispatchArgs {
   const unsigned long long* notify_epoch_ptr;     // count flags (prologue)
   int T, W, me, slot, e_local, ue8m0, ids_i64, nstage;
   int prologue;   // 1: wait for the peers' counts and derive the offsets here (no notify-recv launch)
+  int rotate;     // 1: lane l of the issuing warp serves destination (me + 1 + l) % W instead of l
   unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
 };
 
@@ -197,10 +198,13 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
 
   for (int t = blockIdx.x * kTeams + team; t < a.T; t += gridDim.x * kTeams) {
     // destination set of this token: lane d holds rank d's membership and row (every warp computes it)
+    // lane l serves destination (me + 1 + l) % W when a.rotate is set: the lanes' copies enter the TMA queue in lane
+    // order, so without the rotation every rank would address rank 0 first, then rank 1, ...
     int my_in = 0, my_row = -1;
+    const int my_dst = a.rotate ? (a.me + 1 + lane) % W : lane;
     if (lane < W) {
-      my_in = a.in_rank[(size_t)t * W + lane];
-      if (my_in) my_row = s_send_base[lane] + a.send_off[(size_t)t * W + lane];
+      my_in = a.in_rank[(size_t)t * W + my_dst];
+      if (my_in) my_row = s_send_base[my_dst] + a.send_off[(size_t)t * W + my_dst];
     }
     const unsigned dmask = __ballot_sync(0xffffffffu, my_in);
     if (dmask == 0) continue;  // uniform over the team
@@ -260,7 +264,7 @@ __global__ void __launch_bounds__(kTeams* kTeamThreads, KIND == B200EP_X_BF16_QU
     team_bar(team);
     if (twarp == 0) {
       if (my_in) {
-        char* dst = a.peers.base[lane] + a.slot_off;
+        char* dst = a.peers.base[my_dst] + a.slot_off;
         bulk_s2g(dst + a.plan.off_x + (size_t)my_row * row_bytes, s_row, row_bytes);
         bulk_s2g(dst + a.plan.off_side + (size_t)my_row * side_bytes, s_side, side_bytes);
       }
@@ -949,6 +953,8 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
     a.prologue = (prologue && c->world > 1) ? 1 : 0;
+    static const int rotate_env = getenv("B200EP_HT_ROTATE") ? atoi(getenv("B200EP_HT_ROTATE")) : 0;
+    a.rotate = rotate_env;
     static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
     a.trace = trace_env ? c->local->trace : nullptr;
     // called from b200ep_ht_dispatch_all the layout kernel is queued right in front: start early behind it

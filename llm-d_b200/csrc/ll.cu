@@ -314,7 +314,8 @@ struct LlCombineArgs {
   unsigned long long* trace;  // B200EP_TRACE=1: %globaltimer stamps go here (measurement aid), else null
 };
 
-__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a);
+template <typename Wait>
+__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a, Wait wait);
 
 // a.fused == 1 (all phases in one call): after its pushes every CTA waits for the peers' flags and
 // takes part in the reduction, so the whole combine is one launch.
@@ -424,29 +425,35 @@ __global__ void __launch_bounds__(512) ll_combine_send_kernel(const __grid_const
     }
   }
   if (a.fused) {
-    if ((int)threadIdx.x < W)
-      wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagLlComb, a.slot, threadIdx.x)), want,
-                    kFlagLlComb, a.me, threadIdx.x);
-    __syncthreads();
-    if (blockIdx.x == 0) stamp(13);
-    ll_reduce_items(a);
+    ll_reduce_items(a, [&]() {
+      if ((int)threadIdx.x < W)
+        wait_flag_sys(reinterpret_cast<const uint64_t*>(a.peers.base[a.me] + flag_off(kFlagLlComb, a.slot, threadIdx.x)), want,
+                      kFlagLlComb, a.me, threadIdx.x);
+      __syncthreads();
+      if (blockIdx.x == 0) stamp(13);
+    });
     if (blockIdx.x == 0) stamp(14);
   }
 }
 
 // out[t] = bf16( sum_k w[t,k] * row(t,k) ): fp32 multiply, fp32 add, k ascending.
-// A warp owns (token, 512-byte column block) so that 128 tokens still fill the GPU.
-__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a) {
+// A warp owns (token, 512-byte column block) so that 128 tokens still fill the GPU.  Where the rows of an item are
+// (ids, weights, slots: three dependent loads) is resolved BEFORE `wait` -- the wait for the peers' flags -- for a
+// warp's first item, so that what follows the last flag is one batch of row loads and the stores.
+template <typename Wait>
+__device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a, Wait wait) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
   const int K = a.plan.K, cap = a.plan.cap, e_local = a.plan.e_local;
   const int row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
   const int nblk = (nvec + 31) / 32;
   const char* stage = a.peers.base[a.me] + a.slot_off + a.plan.off_stage;
   const int items = a.T * nblk;
-  for (int it = blockIdx.x * nwarp + warp; it < items; it += gridDim.x * nwarp) {
-    const int t = it / nblk, v = (it % nblk) * 32 + lane;
-    const char* rowp = nullptr;
-    float w = 0.f;
+  const char* rowp = nullptr;
+  float w = 0.f;
+  auto resolve = [&](int it) {
+    const int t = it / nblk;
+    rowp = nullptr;
+    w = 0.f;
     if (lane < K) {
       const long long id = a.ids_i64 ? reinterpret_cast<const long long*>(a.ids)[(size_t)t * K + lane]
                                      : (long long)reinterpret_cast<const int*>(a.ids)[(size_t)t * K + lane];
@@ -459,6 +466,12 @@ __device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a) {
           rowp = stage + ((size_t)t * K + lane) * row_bytes;
       }
     }
+  };
+  int it = blockIdx.x * nwarp + warp;
+  if (it < items) resolve(it);
+  wait();
+  while (it < items) {
+    const int t = it / nblk, v = (it % nblk) * 32 + lane;
     const unsigned kmask = __ballot_sync(0xffffffffu, rowp != nullptr);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int k0 = 0; k0 < K; k0 += 8) {
@@ -492,12 +505,13 @@ __device__ __forceinline__ void ll_reduce_items(const LlCombineArgs& a) {
       st_na_v4(reinterpret_cast<char*>(a.out) + (size_t)t * row_bytes + (size_t)v * 16,
                make_int4((int)o[0], (int)o[1], (int)o[2], (int)o[3]));
     }
+    it += gridDim.x * nwarp;
+    if (it < items) resolve(it);
   }
 }
 
 __global__ void __launch_bounds__(256) ll_combine_recv_kernel(const __grid_constant__ LlCombineArgs a) {
-  cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch_ptr);
-  ll_reduce_items(a);
+  ll_reduce_items(a, [&]() { cta_wait_all_sources(a.peers.base[a.me], a.W, kFlagLlComb, a.slot, a.me, a.epoch_ptr); });
 }
 
 __global__ void ll_wait_sources_kernel(const char* my_base, int W, int cat, int slot, int me,
