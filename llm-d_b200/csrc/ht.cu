@@ -953,7 +953,8 @@ static int dispatch_launch(b200ep_ctx* c, int slot, const void* dev_x, const flo
     a.ue8m0 = ue8m0;
     a.ids_i64 = ids_i64;
     a.prologue = (prologue && c->world > 1) ? 1 : 0;
-    static const int rotate_env = getenv("B200EP_HT_ROTATE") ? atoi(getenv("B200EP_HT_ROTATE")) : 0;
+    // measured at EP=8: dispatch push 248 -> 221 us, whole step 763 -> 734 us (no difference at EP=2)
+    static const int rotate_env = getenv("B200EP_HT_ROTATE") ? atoi(getenv("B200EP_HT_ROTATE")) : 1;
     a.rotate = rotate_env;
     static const int trace_env = getenv("B200EP_TRACE") ? atoi(getenv("B200EP_TRACE")) : 0;
     a.trace = trace_env ? c->local->trace : nullptr;
@@ -1092,12 +1093,17 @@ int ht_combine_args(b200ep_ctx* c, int slot, const void* dev_y, void* dev_out, c
   a.piece_next = &c->local->done[72 + slot * 16];
   a.self_staged = 0;
   const int row_bytes = 2 * H;
-  // DMA pieces: as many whole rows as fit 15 KB (one DeepSeek row; the probe gives 660-665 GB/s for 14 KB pieces and
-  // 677 GB/s for 42 KB ones at EP=8, but small pieces keep the fabric queue shallow and the chunk flags timely)
-  a.rows_per_piece = 15 * 1024 / row_bytes;
+  // DMA pieces: whole rows, up to 45 KB at EP >= 4 (three DeepSeek rows) and 15 KB below.  Measured at EP=8 (whole step,
+  // same build): 1 row 763 us, 2 rows 740 us, 3 rows 709 us together with the rotated dispatch -- the combine ends ~25 us
+  // earlier, the push kernel alone does not change (410 us): fewer, larger pieces leave the reducing warps more of the
+  // L2 / HBM bandwidth and cost fewer queue atomics and mbarrier round trips per byte.  At EP=2 larger pieces were
+  // slightly slower (219.8 vs 218.0 us), hence the split.
+  const int piece_target = (c->world >= 4 ? 45 : 15) * 1024;
+  a.rows_per_piece = piece_target / row_bytes;
   if (a.rows_per_piece < 1) a.rows_per_piece = 1;
   static const int piece_env = getenv("B200EP_HT_PIECE_ROWS") ? atoi(getenv("B200EP_HT_PIECE_ROWS")) : 0;
-  if (piece_env > 0 && (size_t)piece_env * row_bytes * kDmaStages <= 200 * 1024) a.rows_per_piece = piece_env;
+  if (piece_env > 0) a.rows_per_piece = piece_env;
+  while (a.rows_per_piece > 1 && (size_t)a.rows_per_piece * row_bytes * kDmaStages > 200 * 1024) --a.rows_per_piece;
   a.stage_bytes = (unsigned)a.rows_per_piece * (unsigned)row_bytes;
   return B200EP_OK;
 }
