@@ -309,11 +309,128 @@ __device__ __forceinline__ void gather_batch(const char* y, int row_bytes, unsig
 // W > 1, phase SEND.  A warp per (received row, part of the row), two shared-memory stages per warp: gather +
 // reduce into the stage, one TMA bulk copy to stage[me][position] on the source rank (this rank's own rows go to
 // its own stage the same way: the reduction then reads every rank's row from the stage).  Rows are cut into
-// `nparts` parts of at most 8 KB so that twice as many warps fit the shared memory: a warp's work is a chain of
-// dependent memory round trips (one per batch and pair of experts), so the push is fed by warps in flight, not by
-// bytes per warp.  Items interleave the destinations, starting with rank me+1, so that the ranks push along a
-// permutation at any moment.
-__global__ void __launch_bounds__(512, 1) ht_combine_gather_send_kernel(const __grid_constant__ GatherArgs g) {
+// `nparts` parts of at most 8 KB so that more warps fit the shared memory.  A warp's work is a chain of memory
+// round trips, and at EP=8 the fabric takes a part every ~20 us per warp, so the chain is kept short: the next
+// item's ids / weights / rows are fetched while the current one is reduced, and the work of an item is a sequence of
+// (batch, pair of experts) steps whose loads run one step ahead of the accumulation.
+// Items interleave the destinations, starting with rank me+1, so that the ranks push along a permutation.
+__global__ void __launch_bounds__(384, 1) ht_combine_gather_send_kernel(const __grid_constant__ GatherArgs g) {
+  extern __shared__ __align__(128) char s_mem[];
+  __shared__ int s_prefix[kMaxRanks + 1];
+  const HtCombineArgs& a = g.c;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int W = a.W, K = g.K, row_bytes = 2 * a.plan.H, nvec = row_bytes / 16;
+  const int nparts = g.nparts, part_vec = (nvec + nparts - 1) / nparts, part_bytes = part_vec * 16;
+  char* s_stage = s_mem + (size_t)warp * 2 * part_bytes;
+  if ((int)threadIdx.x <= W) s_prefix[threadIdx.x] = a.meta->rank_prefix[threadIdx.x];
+  __syncthreads();
+  int maxcnt = 0;
+  for (int s = 0; s < W; ++s) maxcnt = max(maxcnt, s_prefix[s + 1] - s_prefix[s]);
+  const long long total = (long long)maxcnt * W * nparts, stride = (long long)gridDim.x * nwarp;
+  const char* y = reinterpret_cast<const char*>(a.y);
+
+  struct Item {
+    int s, j, part, dst;  // destination rank, position in its block, part of the row; lane k: grouped row of entry k or -1
+    float w;
+  };
+  // first valid item at or after `it` (a source with fewer rows than the largest block leaves holes), its metadata loads issued
+  auto fetch = [&](long long it, Item& q) -> long long {
+    for (; it < total; it += stride) {
+      const long long rit = it / nparts;
+      q.s = (a.me + 1 + (int)(rit % W)) % W;
+      q.j = (int)(rit / W);
+      if (q.j < s_prefix[q.s + 1] - s_prefix[q.s]) break;
+    }
+    if (it >= total) return total;
+    q.part = (int)(it % nparts);
+    const int m = s_prefix[q.s] + q.j;
+    q.dst = -1;
+    q.w = 0.f;
+    if (lane < K) {  // three independent loads; an entry counts if it has a local expert and a grouped row
+      const long long id = __ldcg(g.recv_idx + (size_t)m * K + lane);
+      const int d = __ldg(g.inv_perm + (size_t)m * K + lane);
+      q.w = __ldcg(g.recv_w + (size_t)m * K + lane);
+      q.dst = id >= 0 ? d : -1;
+    }
+    return it;
+  };
+
+  Item cur, nxt;
+  long long it = fetch((long long)blockIdx.x * nwarp + warp, cur);
+  int n = 0;  // parts this warp has staged
+  while (it < total) {
+    const long long it_next = fetch(it + stride, nxt);  // in flight while this item is reduced
+    const unsigned kmask = __ballot_sync(0xffffffffu, cur.dst >= 0);
+    const int npairs = max(1, (__popc(kmask) + 1) >> 1);
+    char* st = s_stage + (size_t)(n & 1) * part_bytes;
+    ++n;
+    const int vbeg = cur.part * part_vec, vend = min(nvec, vbeg + part_vec);
+    const int nsteps = ((vend - vbeg + 32 * kGatU - 1) / (32 * kGatU)) * npairs;
+    // A step = (batch of kGatU x 32 vectors, pair of the row's experts in k order).  The loads of step i+1 are in
+    // flight while step i is accumulated; a batch is rounded and stored after its last pair.
+    float acc[kGatU][8];
+    auto load = [&](int step, int4 (&r)[2][kGatU]) {
+      const int v0 = vbeg + (step / npairs) * 32 * kGatU, p = step % npairs;
+      const unsigned ka = __fns(kmask, 0, 2 * p + 1), kb = __fns(kmask, 0, 2 * p + 2);
+      const int ra_ = __shfl_sync(0xffffffffu, cur.dst, ka & 31), rb_ = __shfl_sync(0xffffffffu, cur.dst, kb & 31);
+#pragma unroll
+      for (int jj = 0; jj < kGatU; ++jj) {
+        const int v = v0 + jj * 32 + lane;
+        if (v < vend) {
+          if (ka < 32) r[0][jj] = ld_nc_v4(y + (size_t)ra_ * row_bytes + (size_t)v * 16);
+          if (kb < 32) r[1][jj] = ld_nc_v4(y + (size_t)rb_ * row_bytes + (size_t)v * 16);
+        }
+      }
+    };
+    auto accumulate = [&](int step, const int4 (&r)[2][kGatU]) {
+      const int v0 = vbeg + (step / npairs) * 32 * kGatU, p = step % npairs;
+      const unsigned ka = __fns(kmask, 0, 2 * p + 1), kb = __fns(kmask, 0, 2 * p + 2);
+      const float wa = __shfl_sync(0xffffffffu, cur.w, ka & 31), wb = __shfl_sync(0xffffffffu, cur.w, kb & 31);
+#pragma unroll
+      for (int jj = 0; jj < kGatU; ++jj) {
+        if (p == 0) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[jj][i] = 0.f;
+        }
+        const int v = v0 + jj * 32 + lane;
+        if (v < vend) {
+          if (ka < 32) fma8(acc[jj], r[0][jj], wa);
+          if (kb < 32) fma8(acc[jj], r[1][jj], wb);
+          if (p == npairs - 1) reinterpret_cast<int4*>(st)[v - vbeg] = pack8_bf16_rn(acc[jj]);
+        }
+      }
+    };
+    int4 ra[2][kGatU], rb[2][kGatU];
+    load(0, ra);
+    if (lane == 0) bulk_wait_read1();  // the copy that last used this stage has finished reading it
+    __syncwarp();
+    for (int step = 0;;) {
+      if (step + 1 < nsteps) load(step + 1, rb);
+      accumulate(step, ra);
+      if (step + 1 >= nsteps) break;
+      if (step + 2 < nsteps) load(step + 2, ra);
+      accumulate(step + 1, rb);
+      if (step + 2 >= nsteps) break;
+      step += 2;
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(a.peers.base[cur.s] + a.slot_off + stage_row_off(a.plan, a.me, cur.j, row_bytes) + (size_t)vbeg * 16, st,
+               (uint32_t)(vend - vbeg) * 16);
+      bulk_commit();
+    }
+    cur = nxt;
+    it = it_next;
+  }
+  if (lane == 0) bulk_wait_all();
+  cta_done_then_signal(a.done, a.epoch_ptr, a.peers, W, kFlagHtComb, a.slot, a.me);
+}
+
+// The same push without the register double-buffering: 14 warps per SM instead of 12 and fewer instructions per
+// byte.  Used at EP <= 2, where every received row has ~4 local experts and the gather is bound by HBM bandwidth
+// rather than by the length of a warp's chain of round trips (measured at EP=2: 195 us against 226 us pipelined).
+__global__ void __launch_bounds__(512, 1) ht_combine_gather_send_simple_kernel(const __grid_constant__ GatherArgs g) {
   extern __shared__ __align__(128) char s_mem[];
   const HtCombineArgs& a = g.c;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
@@ -531,13 +648,21 @@ extern "C" int b200ep_ht_combine_permuted(b200ep_ctx* c, int slot, const void* d
   if (phases & B200EP_PHASE_SEND) {
     const int nvec = row_bytes / 16;
     g.nparts = (row_bytes + 8191) / 8192;  // parts of at most 8 KB
-    const int part_bytes = (nvec + g.nparts - 1) / g.nparts * 16;
+    const int part_vec = (nvec + g.nparts - 1) / g.nparts;
+    g.nparts = (nvec + part_vec - 1) / part_vec;  // no empty last part
+    const int part_bytes = part_vec * 16;
+    const bool pipelined = c->world >= 4;
     int warps = 200 * 1024 / (2 * part_bytes);
-    if (warps > 16) warps = 16;
+    if (warps > (pipelined ? 12 : 16)) warps = pipelined ? 12 : 16;  // the pipelined kernel double-buffers its loads in registers
     const size_t smem = (size_t)warps * 2 * part_bytes;
     const int grid = c->sm_limit > 0 && c->sm_limit < c->num_sms ? c->sm_limit : c->num_sms;
-    B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_gather_send_kernel, c->device, (int)smem));
-    ht_combine_gather_send_kernel<<<grid, warps * 32, smem, st>>>(g);
+    if (pipelined) {
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_gather_send_kernel, c->device, (int)smem));
+      ht_combine_gather_send_kernel<<<grid, warps * 32, smem, st>>>(g);
+    } else {
+      B200EP_CUDA(ensure_dynamic_smem((const void*)ht_combine_gather_send_simple_kernel, c->device, (int)smem));
+      ht_combine_gather_send_simple_kernel<<<grid, warps * 32, smem, st>>>(g);
+    }
     B200EP_CUDA(cudaGetLastError());
   }
   if (phases & B200EP_PHASE_RECV) return ht_combine_launch_recv(c, g.c, st);
