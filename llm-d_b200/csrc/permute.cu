@@ -38,8 +38,14 @@ namespace b200ep {
 
 constexpr int kPermTile = 256;
 
-__device__ __forceinline__ uint64_t perm_wait_pub(const unsigned long long* p, unsigned tag) {
-  uint64_t v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(p));
+// Per-(block, expert) totals are self-validating words (call tag << 32 | count): a reader needs no acquire, it
+// polls with relaxed loads until the tag is this call's.  Traps instead of hanging.
+__device__ __forceinline__ uint64_t ld_relaxed_gpu_u64(const unsigned long long* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t perm_wait_pub(const unsigned long long* p, unsigned tag, uint64_t v) {
   if ((unsigned)(v >> 32) == tag) return v;
   const long long t0 = clock64();
   do {
@@ -48,7 +54,7 @@ __device__ __forceinline__ uint64_t perm_wait_pub(const unsigned long long* p, u
              (int)blockIdx.x, tag, (unsigned long long)v);
       __trap();
     }
-    v = ld_acquire_gpu_u64(reinterpret_cast<const uint64_t*>(p));
+    v = ld_relaxed_gpu_u64(p);
   } while ((unsigned)(v >> 32) != tag);
   return v;
 }
@@ -70,6 +76,7 @@ __global__ void __launch_bounds__(kPermTile) perm_plan_kernel(const __grid_const
   int* s_start = s_dyn + E * 8;                           // [E + 1]
   int* s_cnt = s_start + E + 1;                           // [E]
   int* s_base = s_cnt + E;                                // [E]
+  int* s_wpre = s_base + E;                               // [E][8]: rows of this block routed to e in the words below w
   __shared__ int s_wtot[8];
   __shared__ unsigned s_bid, s_tag, s_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -131,13 +138,30 @@ __global__ void __launch_bounds__(kPermTile) perm_plan_kernel(const __grid_const
   for (int e = tid; e < E; e += kPermTile) {
     int n = 0;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) n += __popc(s_mask[e * 8 + w]);
+    for (int w = 0; w < 8; ++w) {
+      s_wpre[e * 8 + w] = n;
+      n += __popc(s_mask[e * 8 + w]);
+    }
     st_release_gpu_u64(reinterpret_cast<uint64_t*>(&pub[(size_t)bid * E + e]), ((uint64_t)tag << 32) | (uint32_t)n);
   }
-  // rows of logically earlier blocks per expert
-  for (long long i = tid; i < (long long)bid * E; i += kPermTile) {
-    const int n = (int)(uint32_t)perm_wait_pub(&pub[i], tag);
-    if (n) atomicAdd(&s_base[(int)(i % E)], n);
+  // rows of logically earlier blocks per expert: four independent loads in flight per thread (one dependent load
+  // per word made this loop -- up to bid * E / 256 round trips -- most of the kernel's time)
+  const long long nwords = (long long)bid * E;
+  for (long long i0 = tid; i0 < nwords; i0 += 4 * kPermTile) {
+    uint64_t v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + (long long)u * kPermTile;
+      v[u] = i < nwords ? ld_relaxed_gpu_u64(&pub[i]) : 0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + (long long)u * kPermTile;
+      if (i < nwords) {
+        const int n = (int)(uint32_t)perm_wait_pub(&pub[i], tag, v[u]);
+        if (n) atomicAdd(&s_base[(int)(i % E)], n);
+      }
+    }
   }
   __syncthreads();
   if (m < M) {
@@ -147,8 +171,7 @@ __global__ void __launch_bounds__(kPermTile) perm_plan_kernel(const __grid_const
         int dst = -1;
         const int e = my_e[k];
         if (e >= 0) {
-          int p = __popc(s_mask[e * 8 + warp] & ((1u << lane) - 1u));
-          for (int w = 0; w < warp; ++w) p += __popc(s_mask[e * 8 + w]);
+          const int p = s_wpre[e * 8 + warp] + __popc(s_mask[e * 8 + warp] & ((1u << lane) - 1u));
           dst = s_start[e] + s_base[e] + p;
         }
         a.inv_perm[(size_t)m * K + k] = dst;
@@ -161,17 +184,28 @@ __global__ void __launch_bounds__(kPermTile) perm_plan_kernel(const __grid_const
     printf("b200ep: ht_permute: the grouped layout needs %d rows, the caller's buffers hold %d\n", total, a.m_cap);
     __trap();
   }
-  for (int i = bid * kPermTile + tid; i < a.m_cap; i += gridDim.x * kPermTile) {
-    int id = -1;
+  // every block fills one contiguous chunk of the output rows: one search for a thread's first row, then it walks forward
+  // (start[] is non-decreasing; "the largest e with start[e] <= i" skips experts without rows)
+  {
+    const int chunk = (a.m_cap + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo_row = bid * chunk, hi_row = min(a.m_cap, lo_row + chunk);
+    int i = lo_row + tid, e = 0;
     if (i < total) {
-      int l = 0, h = E - 1;  // largest e with start[e] <= i
+      int l = 0, h = E - 1;
       while (l < h) {
         const int mid = (l + h + 1) >> 1;
         if (s_start[mid] <= i) l = mid; else h = mid - 1;
       }
-      if (i - s_start[l] < s_cnt[l]) id = l;
+      e = l;
     }
-    a.expert_ids[i] = id;
+    for (; i < hi_row; i += kPermTile) {
+      int id = -1;
+      if (i < total) {
+        while (e + 1 < E && s_start[e + 1] <= i) ++e;
+        if (i - s_start[e] < s_cnt[e]) id = e;
+      }
+      a.expert_ids[i] = id;
+    }
   }
   if (a.expert_start && bid == 0)
     for (int i = tid; i <= E; i += kPermTile) a.expert_start[i] = s_start[i];
@@ -581,7 +615,7 @@ extern "C" int b200ep_ht_permute(b200ep_ctx* c, int slot, int alignment, int row
   p.e_local = el;
   p.align = alignment;
   p.m_cap = m_cap;
-  const size_t smem = sizeof(int) * ((size_t)el * 8 + (el + 1) + el + el);
+  const size_t smem = sizeof(int) * ((size_t)el * 8 + (el + 1) + el + el + (size_t)el * 8);
   B200EP_CUDA(ensure_dynamic_smem((const void*)perm_plan_kernel, c->device, (int)smem));
   perm_plan_kernel<<<grid, kPermTile, smem, st>>>(p);
   B200EP_CUDA(cudaGetLastError());
