@@ -679,6 +679,8 @@ def main():
     # ep_gather + Buffer.combine).  Informative: event-timed like the kernels above, max over ranks.
     grouped = None
     try:
+        if parity_res is not None and parity_res.get("ht_grouped") != "ok":
+            raise RuntimeError("the grouped-layout calls failed their oracle check (see parity.ht_grouped): not timed")
         a_perm, s_perm, eids, inv = buf.ht_permute(h, per_expert=last["pe"])
         y_grp = torch.randn(a_perm.shape[0], H, device=dev).to(torch.bfloat16)
         g_perm, g_comb = [], []

@@ -289,9 +289,14 @@ def run_bench_parity(buf, group, W, me, dev, barrier, *, H=7168, E=256, K=8, T_h
     for i, dist_kind in enumerate(("uniform", "one_rank")):
         check_ht(buf, group, W, me, dev, Ts, H, E, K, seed=720 + i, dist=dist_kind, nosync=True)
     res["ht_nosync"] = "ok"
-    for i, dist_kind in enumerate(("uniform", "zipf")):
-        check_ht_grouped(buf, group, W, me, dev, Ts, H, E, K, seed=730 + i, dist=dist_kind, mask_frac=0.1 * i)
-    res["ht_grouped"] = "ok"
+    # the expert-grouped calls are not part of the timed step: a mismatch there is reported (and bench.py then skips their
+    # timing) but does not withhold the step's number.  Every rank reaches the same verdict (_agree is collective).
+    try:
+        for i, dist_kind in enumerate(("uniform", "zipf")):
+            check_ht_grouped(buf, group, W, me, dev, Ts, H, E, K, seed=730 + i, dist=dist_kind, mask_frac=0.1 * i)
+        res["ht_grouped"] = "ok"
+    except ParityError as ex:
+        res["ht_grouped"] = "FAILED: " + str(ex)[:500]
     for ne in ll_experts:
         if ne % W:
             continue
