@@ -99,3 +99,23 @@ def test_unpermute_reduce_matches_a_direct_sum():
     none = ~(ids >= 0).any(1)
     assert none.any() or True
     assert np.all(z[none] == 0)
+
+
+def test_aligned_rows_matches_vllm_compute_aligned_m():
+    """Host-side sizing of the grouped layout == vLLM's compute_aligned_M (fused_moe/deep_gemm_utils.py:26-44) in both of
+    its modes: exact from the per-expert counts, worst case without them; and == the oracle's total."""
+    import pytest
+
+    dgu = pytest.importorskip("vllm.model_executor.layers.fused_moe.deep_gemm_utils")
+    mk = pytest.importorskip("vllm.model_executor.layers.fused_moe.modular_kernel")
+    import torch
+
+    from b200ep import Buffer
+
+    rng = np.random.default_rng(3)
+    for E, M, K in ((32, 21714, 8), (256, 4096, 8), (36, 100, 6), (1, 0, 1)):
+        cnt = rng.integers(0, 900, E).astype(np.int32)
+        meta = mk.ExpertTokensMetadata(expert_num_tokens=torch.from_numpy(cnt), expert_num_tokens_cpu=torch.from_numpy(cnt))
+        want = dgu.compute_aligned_M(M, K, E, 128, meta)
+        assert Buffer.aligned_rows(M, K, E, 128, cnt.tolist()) == want == permute.expert_starts(cnt, 128)[1]
+        assert Buffer.aligned_rows(M, K, E, 128) == dgu.compute_aligned_M(M, K, E, 128, None)
