@@ -462,8 +462,10 @@ __global__ void __launch_bounds__(384, 1) ht_combine_gather_send_kernel(const __
 }
 
 // The same push without the register double-buffering: 14 warps per SM instead of 12 and fewer instructions per
-// byte.  Used at EP <= 2, where every received row has ~4 local experts and the gather is bound by HBM bandwidth
-// rather than by the length of a warp's chain of round trips (measured at EP=2: 195 us against 226 us pipelined).
+// byte.  Used at EP <= 2, where every received row has ~4 local experts and the gather reads ~8x the bytes it pushes,
+// i.e. it is bound by HBM bandwidth rather than by the length of a warp's chain of round trips.  (The EP=2 timings of
+// the two kernels overlap -- 195-289 us for this one over three runs, 221-226 us pipelined over two: the event-timed
+// figure includes the peer's skew -- so the split is by that argument, not by a measured gap.)
 __global__ void __launch_bounds__(512, 1) ht_combine_gather_send_simple_kernel(const __grid_constant__ GatherArgs g) {
   extern __shared__ __align__(128) char s_mem[];
   const HtCombineArgs& a = g.c;
